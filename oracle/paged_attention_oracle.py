@@ -1,0 +1,260 @@
+"""TEST INFRASTRUCTURE ONLY — the parity oracle for the paged-attention hot path.
+
+An independent restatement, in plain fp32 tensor arithmetic, of what the
+reference (baby-llm/baby-sglang, pure Python/PyTorch) computes on the path
+
+    SimpleAttentionBackend.forward        attn_backend.py:8-32
+      MHATokenToKVPool.set_kv_buffer      memory_pool.py:152-171
+      _prefill_attention                  attn_backend.py:34-110
+      _decode_attention                   attn_backend.py:112-149
+    SimplifiedForwardBatch factories      forward_batch.py:24-84
+
+The arithmetic itself lives in a third-party dependency of the reference,
+PyTorch (`requirements.txt:1`, `torch>=2.0.0`, not vendored; 2.11.0 here):
+`F.scaled_dot_product_attention`, whose published semantics are
+`softmax(Q K^T / sqrt(D) + bias) V` with the softmax and accumulation done in
+fp32 for half inputs.  This file restates exactly that, with explicit loops over
+requests and no call to SDPA, so a bug shared with the reference's call chain
+would show up.
+
+Pinning.  The reference ships no tests, golden vectors or fixtures for this
+path, so the pin is the reference itself: `tests/golden/` holds
+outputs of the reference's own modules run in the build container
+(`tests/golden/make_golden.py` generated them by importing `/root/reference`),
+and `tests/test_oracle_vs_golden.py` checks every function here against them.
+`tests/test_oracle_vs_reference.py` repeats the check against the live
+reference whenever a checkout is reachable.
+
+Index/byte work (kv_store, metadata, plans) is bit-exact by construction;
+floating-point work is fp32 and is compared with a tolerance stated in the tests.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Optional, Tuple
+
+import torch
+
+# --------------------------------------------------------------------------------------
+# K1  kv_store   (memory_pool.py:152-171)
+# --------------------------------------------------------------------------------------
+
+
+def kv_store(k_slab: torch.Tensor, v_slab: torch.Tensor, loc: torch.Tensor,
+             cache_k: torch.Tensor, cache_v: torch.Tensor) -> None:
+    """slab[loc[t]] = row t, for K and V, after a round-to-nearest cast to the slab dtype.
+
+    Follows memory_pool.py:159-171: `loc` is widened to int64 (:159-160), the sources
+    are cast to the pool dtype when they differ (:163-165), then two index-puts (:170-171).
+    Written here as an explicit per-token loop so duplicates resolve "last writer wins"
+    deterministically (the reference leaves duplicates undefined; callers never produce
+    them: slots come from a free list).
+    """
+    T = int(loc.shape[0])
+    loc64 = loc.to(torch.int64).tolist()
+    ck = cache_k.to(k_slab.dtype)
+    cv = cache_v.to(v_slab.dtype)
+    for t in range(T):
+        k_slab[loc64[t]] = ck[t]
+        v_slab[loc64[t]] = cv[t]
+
+
+# --------------------------------------------------------------------------------------
+# the attention arithmetic (what SDPA is documented to do), fp32
+# --------------------------------------------------------------------------------------
+
+
+def _gqa_attend(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, first_row_limit: int,
+                acc_dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    """q [n, Hq, D], k/v [full, Hkv, D].  Row i of q sees columns 0..first_row_limit+i (inclusive).
+
+    q head h reads kv head h // (Hq // Hkv)  — `repeat_interleave(G, dim=1)` at
+    attn_backend.py:61-66 / :130-135.  Scale is 1/sqrt(D): the reference accepts
+    `scaling` but never forwards it (attn_backend.py:18,94-101,141-143), so SDPA's
+    default applies.
+    """
+    n, Hq, D = q.shape
+    full, Hkv, _ = k.shape
+    G = Hq // Hkv
+    qf = q.to(acc_dtype)
+    kf = k.to(acc_dtype)
+    vf = v.to(acc_dtype)
+    scale = 1.0 / math.sqrt(D)
+    out = torch.empty((n, Hq, D), dtype=acc_dtype, device=q.device)
+    cols = torch.arange(full, device=q.device)
+    rows = torch.arange(n, device=q.device)
+    # True where masked: col > prefix + row   (attn_backend.py:83-85)
+    masked = cols[None, :] > (first_row_limit + rows)[:, None]
+    for h in range(Hq):
+        s = (qf[:, h, :] @ kf[:, h // G, :].T) * scale           # [n, full]
+        s = s.masked_fill(masked, float("-inf"))
+        m = s.max(dim=-1, keepdim=True).values
+        p = torch.exp(s - m)
+        p = p / p.sum(dim=-1, keepdim=True)
+        out[:, h, :] = p @ vf[:, h // G, :]
+    return out
+
+
+def decode_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor,
+                     req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                     seq_lens: torch.Tensor, out_dtype: Optional[torch.dtype] = None,
+                     acc_dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    """attn_backend.py:112-149.  q [B, Hq, D] -> [B, Hq*D].
+
+    `seq_lens[i]` already counts the token being decoded (scheduler.py:489-490); its K/V
+    row was stored before this call (attn_backend.py:20-23), so the new token attends to
+    itself through `req_to_token[r, seq-1]`.
+    """
+    B, Hq, D = q.shape
+    out_dtype = out_dtype or q.dtype
+    outs = []
+    for i in range(B):
+        n = int(seq_lens[i])
+        r = int(req_pool_indices[i])
+        idx = req_to_token[r, :n].to(torch.int64)                 # :122-125
+        o = _gqa_attend(q[i:i + 1], k_slab[idx], v_slab[idx], first_row_limit=n - 1,
+                        acc_dtype=acc_dtype)
+        outs.append(o.reshape(1, Hq * D))
+    if not outs:
+        return q.new_zeros((0, Hq * D), dtype=out_dtype)
+    return torch.cat(outs, dim=0).to(out_dtype)
+
+
+def extend_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor,
+                     req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                     seq_lens: torch.Tensor, prefix_lens: torch.Tensor,
+                     extended_lens: torch.Tensor, out_dtype: Optional[torch.dtype] = None,
+                     acc_dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    """attn_backend.py:34-110.  q [sum(ext), Hq, D] packed in request order -> [sum(ext), Hq*D].
+
+    Request i owns q rows [off, off+ext_i); row j sees the whole prefix plus new tokens
+    0..j (mask `col > prefix + row`, :83-85).  K/V for prefix AND new tokens are read back
+    from the pool (:55-59).  ext_i == 0 contributes nothing (:44-46); an empty batch gives
+    a [0, Hq*D] tensor (:108-109).
+    """
+    T, Hq, D = q.shape
+    out_dtype = out_dtype or q.dtype
+    outs = []
+    off = 0
+    for i in range(int(req_pool_indices.shape[0])):
+        ext = int(extended_lens[i])
+        if ext == 0:
+            continue
+        pre = int(prefix_lens[i])
+        full = int(seq_lens[i])
+        r = int(req_pool_indices[i])
+        idx = req_to_token[r, :full].to(torch.int64)
+        o = _gqa_attend(q[off:off + ext], k_slab[idx], v_slab[idx], first_row_limit=pre,
+                        acc_dtype=acc_dtype)
+        outs.append(o.reshape(ext, Hq * D))
+        off += ext
+    if not outs:
+        return q.new_zeros((0, Hq * D), dtype=out_dtype)
+    return torch.cat(outs, dim=0).to(out_dtype)
+
+
+def backend_forward(q, k, v, k_slab, v_slab, req_to_token, req_pool_indices, seq_lens,
+                    out_cache_loc, is_prefill: bool, prefix_lens=None, extended_lens=None,
+                    save_kv_cache: bool = True, out_dtype=None, acc_dtype=torch.float32):
+    """attn_backend.py:8-32: store first (:20-23), then attend (:25-32)."""
+    if save_kv_cache and k is not None and v is not None:
+        kv_store(k_slab, v_slab, out_cache_loc, k, v)
+    if is_prefill:
+        return extend_attention(q, k_slab, v_slab, req_to_token, req_pool_indices, seq_lens,
+                                prefix_lens, extended_lens, out_dtype, acc_dtype)
+    return decode_attention(q, k_slab, v_slab, req_to_token, req_pool_indices, seq_lens,
+                            out_dtype, acc_dtype)
+
+
+# --------------------------------------------------------------------------------------
+# K4  batch metadata  (forward_batch.py:24-84 plus the device-built additions)
+# --------------------------------------------------------------------------------------
+
+
+@dataclass
+class OracleMetadata:
+    extended_lens: Optional[torch.Tensor]   # int64 [B]   (prefill only)
+    positions: torch.Tensor                 # int64 [T]
+    qo_indptr: torch.Tensor                 # int32 [B+1]
+    kv_indptr: torch.Tensor                 # int32 [B+1]
+    kv_indices: torch.Tensor                # int32 [sum(seq)]
+
+
+def build_metadata(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                   seq_lens: torch.Tensor, prefix_lens: Optional[torch.Tensor]) -> OracleMetadata:
+    """Decode (prefix_lens None): positions = seq_lens - 1 (forward_batch.py:72), one q row each.
+    Prefill: extended = seq - prefix (:36-38); positions = prefix..prefix+ext-1 per request,
+    concatenated (:40-45).  kv_indptr / kv_indices are the CSR flattening of
+    `req_to_token[r, :seq]` the attention loops read (attn_backend.py:55-57,123-125).
+    """
+    B = int(req_pool_indices.shape[0])
+    seq = [int(x) for x in seq_lens]
+    if prefix_lens is None:
+        ext_list = [1] * B
+        pos = [s - 1 for s in seq]
+        extended = None
+    else:
+        pre = [int(x) for x in prefix_lens]
+        ext_list = [s - p for s, p in zip(seq, pre)]
+        pos = []
+        for p, e in zip(pre, ext_list):
+            pos.extend(range(p, p + e))
+        extended = torch.tensor(ext_list, dtype=torch.int64)
+    qo = [0]
+    kv = [0]
+    for e, s in zip(ext_list, seq):
+        qo.append(qo[-1] + e)
+        kv.append(kv[-1] + s)
+    rows = [req_to_token[int(req_pool_indices[i]), :seq[i]].to(torch.int32).cpu() for i in range(B)]
+    kv_indices = torch.cat(rows) if rows else torch.zeros(0, dtype=torch.int32)
+    return OracleMetadata(
+        extended_lens=extended,
+        positions=torch.tensor(pos, dtype=torch.int64),
+        qo_indptr=torch.tensor(qo, dtype=torch.int32),
+        kv_indptr=torch.tensor(kv, dtype=torch.int32),
+        kv_indices=kv_indices,
+    )
+
+
+# --------------------------------------------------------------------------------------
+# split-KV plan (no reference counterpart: the reference never splits; this restates the
+# partition the CUDA decode kernel uses so the plan kernel can be checked bit-exactly)
+# --------------------------------------------------------------------------------------
+
+
+def split_plan(kv_lens, n_head_groups: int, tile_tokens: int, n_ctas: int):
+    """Flatten (row, head_group) "sequences" into `tile_tokens`-token tiles and cut the tile
+    space into `n_ctas` equal contiguous ranges.
+
+    Returns (tile_indptr [NS+1], cta_tile_begin [n_ctas+1], cta_first_seq [n_ctas+1]).
+    Sequence j = row * n_head_groups + head_group owns tiles [tile_indptr[j], tile_indptr[j+1]).
+    CTA c owns tiles [floor(c*NT/n_ctas), floor((c+1)*NT/n_ctas)); cta_first_seq[c] is the
+    sequence holding its first tile (NS when the CTA has no tiles to its right).
+    """
+    tile_indptr = [0]
+    for n in kv_lens:
+        nt = (int(n) + tile_tokens - 1) // tile_tokens
+        for _ in range(n_head_groups):
+            tile_indptr.append(tile_indptr[-1] + nt)
+    NT = tile_indptr[-1]
+    NS = len(tile_indptr) - 1
+    begins = [(c * NT) // n_ctas for c in range(n_ctas + 1)]
+    first = []
+    j = 0
+    for c in range(n_ctas + 1):
+        t = begins[c]
+        while j < NS and tile_indptr[j + 1] <= t:
+            j += 1
+        first.append(j)
+    return tile_indptr, begins, first
+
+
+def merge_partials(o_parts: torch.Tensor, lse2_parts: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """LSE merge of split-KV partials.  o_parts [P, H, D] normalised partial outputs,
+    lse2_parts [P, H] base-2 log-sum-exp of each part's scores.  Returns (o [H, D], lse2 [H])."""
+    m = lse2_parts.max(dim=0).values
+    w = torch.exp2(lse2_parts - m[None, :])
+    den = w.sum(dim=0)
+    o = (w[:, :, None] * o_parts).sum(dim=0) / den[:, None]
+    return o, m + torch.log2(den)
