@@ -1,0 +1,284 @@
+"""Tensor-level wrappers over the C ABI (include/bsgl_b200.h).
+
+PyTorch is plumbing here: it owns device memory and the current stream; every function below
+validates its tensors, allocates outputs/workspaces from torch's stream-ordered caching
+allocator and hands raw pointers plus `torch.cuda.current_stream()` to the library.  Nothing
+here computes: without a CUDA device and the built library these functions raise.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+_DTYPE_CODE = {torch.bfloat16: _lib.BF16, torch.float16: _lib.F16, torch.float32: _lib.F32}
+_SM_COUNT = {}
+#: counts launches issued through this module (bench.py reports it as `gpu_launches`)
+LAUNCH_COUNT = 0
+
+
+def _count(n: int = 1) -> None:
+    global LAUNCH_COUNT
+    LAUNCH_COUNT += n
+
+
+def _require_cuda(*tensors: torch.Tensor) -> torch.device:
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise _lib.BsglError(
+                "baby_sglang_b200 runs on CUDA tensors only (got a %s tensor); there is no CPU path" % t.device)
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise _lib.BsglError(f"tensors on different devices: {dev} vs {t.device}")
+    return dev
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def dtype_code(dt: torch.dtype) -> int:
+    try:
+        return _DTYPE_CODE[dt]
+    except KeyError:
+        raise _lib.BsglError(f"unsupported dtype {dt}") from None
+
+
+def sm_count(device: Optional[torch.device] = None) -> int:
+    idx = torch.cuda.current_device() if device is None or device.index is None else device.index
+    if idx not in _SM_COUNT:
+        _SM_COUNT[idx] = torch.cuda.get_device_properties(idx).multi_processor_count
+    return _SM_COUNT[idx]
+
+
+def heads_per_group(n_kv_heads: int) -> int:
+    return _lib.load().bsgl_heads_per_group(int(n_kv_heads))
+
+
+# --------------------------------------------------------------------------------------- K1
+def kv_store(k_slab: torch.Tensor, v_slab: torch.Tensor, loc: torch.Tensor,
+             cache_k: torch.Tensor, cache_v: torch.Tensor) -> None:
+    """slab[loc[t]] = (cache_k[t], cache_v[t]); replaces memory_pool.py:152-171.
+
+    `loc` is the int32 `out_cache_loc`; `cache_v` may be a strided view of the fused QKV output
+    (qwen2.py:285-290).  Sources in another float dtype are cast round-to-nearest in the kernel.
+    """
+    _require_cuda(k_slab, v_slab, loc, cache_k, cache_v)
+    T = int(loc.shape[0])
+    if T == 0:
+        return
+    S1, H, D = k_slab.shape
+    if not (k_slab.is_contiguous() and v_slab.is_contiguous()):
+        raise _lib.BsglError("KV slabs must be contiguous [S+1, H, D]")
+    if loc.dtype != torch.int32:
+        loc = loc.to(torch.int32)
+    if not loc.is_contiguous():
+        loc = loc.contiguous()
+    if cache_v.dtype != cache_k.dtype:
+        cache_v = cache_v.to(cache_k.dtype)
+    cache_k = cache_k.reshape(T, H, D) if cache_k.dim() != 3 else cache_k
+    cache_v = cache_v.reshape(T, H, D) if cache_v.dim() != 3 else cache_v
+    esz = cache_k.element_size()
+    align = 16 // esz
+
+    def _ok(t):
+        return (t.stride(2) == 1 and t.stride(0) % align == 0 and t.stride(1) % align == 0
+                and t.data_ptr() % 16 == 0)
+
+    if not _ok(cache_k):
+        cache_k = cache_k.contiguous()
+    if not _ok(cache_v):
+        cache_v = cache_v.contiguous()
+    lib = _lib.load()
+    rc = lib.bsgl_kv_store(k_slab.data_ptr(), v_slab.data_ptr(), loc.data_ptr(), cache_k.data_ptr(),
+                           cache_v.data_ptr(), T, H, D, cache_k.stride(0), cache_k.stride(1),
+                           cache_v.stride(0), cache_v.stride(1), dtype_code(cache_k.dtype),
+                           dtype_code(k_slab.dtype), _stream())
+    _lib.check(rc, "bsgl_kv_store")
+    _count()
+
+
+# --------------------------------------------------------------------------------------- K4
+@dataclass
+class AttnPlan:
+    """Device-resident description of one batch for the paged-attention kernel (built by K4)."""
+    n_rows: int
+    n_kv_heads: int
+    n_head_groups: int
+    n_ctas: int
+    row_idx_off: torch.Tensor      # int64 [rows]
+    row_kv_len: torch.Tensor       # int32 [rows]
+    plan_hdr: torch.Tensor         # int32 [4]  {n_tiles, n_ctas_eff, n_seqs, 0}
+    tile_indptr: torch.Tensor      # int32 [rows*nhg + 1]
+    cta_first_seq: torch.Tensor    # int32 [n_ctas + 1]
+
+
+@dataclass
+class BatchMetadata:
+    positions: torch.Tensor                    # int64 [T]
+    kv_indptr: torch.Tensor                    # int32 [B+1]
+    qo_indptr: torch.Tensor                    # int32 [B+1]
+    extended_lens: Optional[torch.Tensor]      # int64 [B] (extend only)
+    plan: Optional[AttnPlan]
+    kv_indices: Optional[torch.Tensor] = None  # int32 [sum(seq)] (built on request)
+
+
+def _plan_buffers(dev, n_rows: int, nhg: int, n_ctas: int):
+    i32 = dict(dtype=torch.int32, device=dev)
+    return (torch.empty(n_rows, dtype=torch.int64, device=dev), torch.empty(n_rows, **i32),
+            torch.empty(_lib.PLAN_HDR_INTS, **i32), torch.empty(n_rows * nhg + 1, **i32),
+            torch.empty(n_ctas + 1, **i32))
+
+
+def _as_i64(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.int64:
+        t = t.to(torch.int64)
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def build_decode_metadata(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                          seq_lens: torch.Tensor, n_kv_heads: int,
+                          n_ctas: Optional[int] = None) -> BatchMetadata:
+    """Device-side replacement of create_decode_batch's host work (forward_batch.py:61-84) and of
+    the per-request `.item()` chain in `_decode_attention` (attn_backend.py:117-125)."""
+    dev = _require_cuda(req_to_token, req_pool_indices, seq_lens)
+    B = int(req_pool_indices.shape[0])
+    nhg = int(n_kv_heads) // heads_per_group(n_kv_heads)
+    n_ctas = n_ctas or sm_count(dev)
+    rpi, sl = _as_i64(req_pool_indices), _as_i64(seq_lens)
+    positions = torch.empty(B, dtype=torch.int64, device=dev)
+    kv_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
+    qo_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
+    row_idx_off, row_kv_len, plan_hdr, tile_indptr, cta_first_seq = _plan_buffers(dev, B, nhg, n_ctas)
+    rc = _lib.load().bsgl_build_decode_metadata(
+        req_to_token.stride(0), rpi.data_ptr(), sl.data_ptr(), B, nhg, n_ctas, positions.data_ptr(),
+        kv_indptr.data_ptr(), qo_indptr.data_ptr(), row_idx_off.data_ptr(), row_kv_len.data_ptr(),
+        plan_hdr.data_ptr(), tile_indptr.data_ptr(), cta_first_seq.data_ptr(), _stream())
+    _lib.check(rc, "bsgl_build_decode_metadata")
+    _count()
+    plan = AttnPlan(B, int(n_kv_heads), nhg, n_ctas, row_idx_off, row_kv_len, plan_hdr, tile_indptr, cta_first_seq)
+    return BatchMetadata(positions, kv_indptr, qo_indptr, None, plan)
+
+
+def build_extend_metadata(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                          seq_lens: torch.Tensor, prefix_lens: torch.Tensor, n_tokens: int,
+                          n_kv_heads: int, n_ctas: Optional[int] = None,
+                          row_plan: bool = True) -> BatchMetadata:
+    """Device-side replacement of create_prefill_batch's host loop (forward_batch.py:36-45) and of
+    the per-request `.item()` chain in `_prefill_attention` (attn_backend.py:43-57).  `n_tokens`
+    (= q rows) is known on the host: it is `input_ids.shape[0]`."""
+    dev = _require_cuda(req_to_token, req_pool_indices, seq_lens, prefix_lens)
+    B = int(req_pool_indices.shape[0])
+    T = int(n_tokens)
+    nhg = int(n_kv_heads) // heads_per_group(n_kv_heads)
+    n_ctas = n_ctas or sm_count(dev)
+    rpi, sl, pl = _as_i64(req_pool_indices), _as_i64(seq_lens), _as_i64(prefix_lens)
+    extended = torch.empty(B, dtype=torch.int64, device=dev)
+    positions = torch.empty(T, dtype=torch.int64, device=dev)
+    kv_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
+    qo_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
+    row_idx_off, row_kv_len, plan_hdr, tile_indptr, cta_first_seq = _plan_buffers(dev, T, nhg, n_ctas)
+    null = ctypes.c_void_p(0)
+    rc = _lib.load().bsgl_build_extend_metadata(
+        req_to_token.stride(0), rpi.data_ptr(), sl.data_ptr(), pl.data_ptr(), B, T, nhg, n_ctas,
+        extended.data_ptr(), positions.data_ptr(), qo_indptr.data_ptr(), kv_indptr.data_ptr(),
+        row_idx_off.data_ptr(), row_kv_len.data_ptr(),
+        plan_hdr.data_ptr() if row_plan else null, tile_indptr.data_ptr() if row_plan else null,
+        cta_first_seq.data_ptr() if row_plan else null, _stream())
+    _lib.check(rc, "bsgl_build_extend_metadata")
+    _count()
+    plan = AttnPlan(T, int(n_kv_heads), nhg, n_ctas, row_idx_off, row_kv_len, plan_hdr, tile_indptr,
+                    cta_first_seq) if row_plan else None
+    return BatchMetadata(positions, kv_indptr, qo_indptr, extended, plan)
+
+
+def gather_kv_indices(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                      kv_indptr: torch.Tensor, total_kv: int) -> torch.Tensor:
+    """CSR flattening of `req_to_token[r, :seq]` (the slices at attn_backend.py:55-57,123-125)."""
+    dev = _require_cuda(req_to_token, req_pool_indices, kv_indptr)
+    out = torch.empty(int(total_kv), dtype=torch.int32, device=dev)
+    rpi = _as_i64(req_pool_indices)
+    rc = _lib.load().bsgl_gather_kv_indices(req_to_token.data_ptr(), req_to_token.stride(0), rpi.data_ptr(),
+                                            kv_indptr.data_ptr(), int(rpi.shape[0]), out.data_ptr(), _stream())
+    _lib.check(rc, "bsgl_gather_kv_indices")
+    _count()
+    return out
+
+
+# --------------------------------------------------------------------------------------- K2
+def partial_buffers(dev, n_ctas: int, n_q_heads: int, n_kv_heads: int, head_dim: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    o = ctypes.c_int64(0)
+    l = ctypes.c_int64(0)
+    rc = _lib.load().bsgl_partial_sizes(n_ctas, n_q_heads, n_kv_heads, head_dim, ctypes.byref(o), ctypes.byref(l))
+    _lib.check(rc, "bsgl_partial_sizes")
+    return (torch.empty(o.value, dtype=torch.float32, device=dev),
+            torch.empty(l.value, dtype=torch.float32, device=dev))
+
+
+def paged_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor, idx_base: torch.Tensor,
+                    plan: AttnPlan, sm_scale: float, out: Optional[torch.Tensor] = None,
+                    workspace: Optional[Tuple[torch.Tensor, torch.Tensor]] = None,
+                    merge: bool = True) -> torch.Tensor:
+    """One q row per plan row over the paged KV; returns [rows, Hq*D] in q's dtype.
+
+    Replaces `_decode_attention` (attn_backend.py:112-149): K2 split-KV partial pass + K2c merge.
+    `idx_base` is the int32 page table (`req_to_token`) or a flattened `kv_indices`.
+    """
+    dev = _require_cuda(q, k_slab, v_slab, idx_base)
+    if q.dim() != 3:
+        raise _lib.BsglError(f"q must be [rows, Hq, D], got {tuple(q.shape)}")
+    rows, Hq, D = q.shape
+    if rows != plan.n_rows:
+        raise _lib.BsglError(f"q has {rows} rows but the plan was built for {plan.n_rows}")
+    Hkv = int(k_slab.shape[1])
+    if Hkv != plan.n_kv_heads or int(k_slab.shape[2]) != D:
+        raise _lib.BsglError("KV slab geometry does not match q / plan")
+    if q.dtype != k_slab.dtype or q.dtype != v_slab.dtype:
+        raise _lib.BsglError(f"q dtype {q.dtype} != KV slab dtype {k_slab.dtype}")
+    if idx_base.dtype != torch.int32:
+        raise _lib.BsglError("page table must be int32")
+    if not q.is_contiguous():
+        q = q.contiguous()
+    if out is None:
+        out = torch.empty((rows, Hq * D), dtype=q.dtype, device=dev)
+    if rows == 0:
+        return out
+    part_o, part_lse = workspace if workspace is not None else partial_buffers(dev, plan.n_ctas, Hq, Hkv, D)
+    lib = _lib.load()
+    code = dtype_code(q.dtype)
+    st = _stream()
+    rc = lib.bsgl_paged_attention(
+        q.data_ptr(), k_slab.data_ptr(), v_slab.data_ptr(), idx_base.data_ptr(), plan.row_idx_off.data_ptr(),
+        plan.row_kv_len.data_ptr(), plan.plan_hdr.data_ptr(), plan.tile_indptr.data_ptr(),
+        plan.cta_first_seq.data_ptr(), rows, Hq, Hkv, D, float(sm_scale), code, out.data_ptr(),
+        part_o.data_ptr(), part_lse.data_ptr(), plan.n_ctas, st)
+    _lib.check(rc, "bsgl_paged_attention")
+    _count()
+    if merge:
+        rc = lib.bsgl_merge_partials(part_o.data_ptr(), part_lse.data_ptr(), plan.plan_hdr.data_ptr(),
+                                     plan.tile_indptr.data_ptr(), rows, Hq, Hkv, D, code, out.data_ptr(), st)
+        _lib.check(rc, "bsgl_merge_partials")
+        _count()
+    return out
+
+
+# --------------------------------------------------------------------------------------- K3
+def extend_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor, forward_batch,
+                     md: BatchMetadata, sm_scale: float) -> torch.Tensor:
+    """Ragged extend (reference `_prefill_attention`, attn_backend.py:34-110).
+
+    Row-wise formulation: q token t of request i is a sequence of prefix_i + r + 1 KV tokens over
+    request i's page-table row, which is exactly the causal-within-extend mask `col <= prefix+row`
+    (attn_backend.py:83-85); it runs on the split-KV kernel with the per-row plan K4 built.
+    """
+    if md.plan is None:
+        raise _lib.BsglError("extend metadata was built without a row plan")
+    return paged_attention(q, k_slab, v_slab, forward_batch.req_to_token_pool.req_to_token, md.plan, sm_scale)

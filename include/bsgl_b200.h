@@ -1,0 +1,154 @@
+/*
+ * bsgl_b200 — C ABI of the B200-native paged-attention path for baby-sglang.
+ *
+ * This is the drop-in boundary: plain pointers, sizes and a CUDA stream handle; no torch
+ * types.  Every entry point returns 0 on success and a non-zero code on failure, in which
+ * case bsgl_last_error() (thread-local) describes it.  All device pointers are BORROWED for
+ * stream-ordered work only: the library never allocates, frees or retains them, holds no
+ * process-global device scratch, and launches on the `stream` it is given (the reference runs
+ * this path on a worker thread under a non-default stream, overlap_worker.py:104-106).
+ *
+ * What each entry point replaces in the reference (paths relative to baby-llm/baby-sglang):
+ *
+ *   bsgl_kv_store               MHATokenToKVPool.set_kv_buffer            memory_pool.py:152-171
+ *   bsgl_build_decode_metadata  SimplifiedForwardBatch.create_decode_batch forward_batch.py:61-84
+ *                               + the per-request .item()/slice chain      attn_backend.py:117-125
+ *   bsgl_build_extend_metadata  SimplifiedForwardBatch.create_prefill_batch forward_batch.py:24-59
+ *                               + the per-request .item()/slice chain      attn_backend.py:43-57
+ *   bsgl_gather_kv_indices      req_to_token[r, :seq] flattening           attn_backend.py:55-57,123-125
+ *   bsgl_paged_attention        _decode_attention (gather, GQA expand,     attn_backend.py:112-149
+ *                               SDPA, cat) — split-KV partial pass; also
+ *                               row-wise extend for short extends          attn_backend.py:34-110
+ *   bsgl_merge_partials         (no counterpart: LSE merge of the split-KV partials)
+ *   bsgl_extend_attention       _prefill_attention                         attn_backend.py:34-110
+ *
+ * Layout conventions (identical to the reference's tensors):
+ *   q        [rows, n_q_heads, head_dim]            contiguous, bf16 or fp16
+ *   k/v slab [S+1, n_kv_heads, head_dim]            contiguous, slot 0 is the pad slot
+ *   out      [rows, n_q_heads*head_dim]             contiguous, q's dtype
+ *   page table req_to_token [max_reqs, C] int32, req_pool_indices int64, seq_lens int64,
+ *   out_cache_loc int32 (forward_batch.py:10-22 as probed in SURVEY.md §8a).
+ *   q head h reads kv head h / (n_q_heads / n_kv_heads).  Softmax scale is passed explicitly;
+ *   the reference's effective value is head_dim^-0.5 (it never forwards `scaling`,
+ *   attn_backend.py:18,94-101).
+ */
+#ifndef BSGL_B200_H_
+#define BSGL_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BSGL_VERSION 100       /* 0.1.0 */
+#define BSGL_TILE_TOKENS 16    /* KV tokens per pipeline tile of the paged-attention kernel */
+#define BSGL_MIN_TILES_PER_CTA 4
+#define BSGL_PLAN_HDR_INTS 4   /* plan_hdr = { n_tiles, n_ctas_eff, n_seqs, reserved } */
+
+enum bsgl_dtype { BSGL_BF16 = 0, BSGL_F16 = 1, BSGL_F32 = 2 };
+
+enum bsgl_status {
+  BSGL_OK = 0,
+  BSGL_ERR_INVALID = 1,      /* bad argument (null pointer, unsupported shape/dtype, misalignment) */
+  BSGL_ERR_CUDA = 2,         /* a CUDA runtime call or launch failed */
+  BSGL_ERR_UNSUPPORTED = 3   /* valid request this build has no kernel for */
+};
+
+int bsgl_version(void);
+/* Thread-local description of the last failure on the calling thread ("" if none). */
+const char* bsgl_last_error(void);
+/* Number of SMs on the current CUDA device (used to size the persistent grids). */
+int bsgl_sm_count(int* out_sm_count);
+/* KV heads one CTA of the paged-attention kernel handles (the "head group" width) for a pool
+ * with n_kv_heads heads: the largest of {4,2,1} dividing n_kv_heads. */
+int bsgl_heads_per_group(int n_kv_heads);
+
+/* K1.  slab[loc[t], h, :] = src[t, h, :] for K and V in one launch.  Source rows may be
+ * strided views (the reference hands `v` as a view of the fused QKV output, qwen2.py:285-290):
+ * strides are in ELEMENTS; the innermost dimension must be contiguous.  src_dtype may differ
+ * from slab_dtype (round-to-nearest-even cast, memory_pool.py:163-165).  Bit-exact. */
+int bsgl_kv_store(void* k_slab, void* v_slab, const int32_t* loc,
+                  const void* k_src, const void* v_src,
+                  int64_t n_tokens, int n_kv_heads, int head_dim,
+                  int64_t k_row_stride, int64_t k_head_stride,
+                  int64_t v_row_stride, int64_t v_head_stride,
+                  int src_dtype, int slab_dtype, void* stream);
+
+/* K4 (decode).  One q row per request.  Outputs (all device, caller-allocated):
+ *   positions   int64 [B]      = seq_lens - 1                      forward_batch.py:72
+ *   kv_indptr   int32 [B+1]    exclusive cumsum of seq_lens
+ *   qo_indptr   int32 [B+1]    0..B
+ *   row_idx_off int64 [B]      element offset of the row's token list inside req_to_token
+ *   row_kv_len  int32 [B]      KV tokens the row attends to (= seq_lens)
+ *   plan_hdr    int32 [4], tile_indptr int32 [B*n_head_groups+1], cta_first_seq int32 [n_ctas+1]
+ *                              the split-KV plan for bsgl_paged_attention */
+int bsgl_build_decode_metadata(int64_t page_table_stride, const int64_t* req_pool_indices,
+                               const int64_t* seq_lens, int batch, int n_head_groups, int n_ctas,
+                               int64_t* positions, int32_t* kv_indptr, int32_t* qo_indptr,
+                               int64_t* row_idx_off, int32_t* row_kv_len,
+                               int32_t* plan_hdr, int32_t* tile_indptr, int32_t* cta_first_seq,
+                               void* stream);
+
+/* K4 (extend / prefill).  n_tokens = sum(seq_lens - prefix_lens) is known on the host (it is
+ * q.shape[0]).  Outputs:
+ *   extended_lens int64 [B]    = seq_lens - prefix_lens            forward_batch.py:36-38
+ *   positions     int64 [T]    prefix..prefix+ext-1 per request    forward_batch.py:40-45
+ *   qo_indptr     int32 [B+1], kv_indptr int32 [B+1]
+ *   row_idx_off   int64 [T], row_kv_len int32 [T]  per q token: its request's page-table row
+ *                              and prefix + local_row + 1 (mask col <= prefix+row, attn_backend.py:83-85)
+ *   plan_hdr / tile_indptr [T*n_head_groups+1] / cta_first_seq [n_ctas+1]: row-wise plan
+ *                              (may be NULL when the row-wise kernel will not be used). */
+int bsgl_build_extend_metadata(int64_t page_table_stride, const int64_t* req_pool_indices,
+                               const int64_t* seq_lens, const int64_t* prefix_lens, int batch,
+                               int64_t n_tokens, int n_head_groups, int n_ctas,
+                               int64_t* extended_lens, int64_t* positions,
+                               int32_t* qo_indptr, int32_t* kv_indptr,
+                               int64_t* row_idx_off, int32_t* row_kv_len,
+                               int32_t* plan_hdr, int32_t* tile_indptr, int32_t* cta_first_seq,
+                               void* stream);
+
+/* kv_indices[kv_indptr[i] + p] = req_to_token[req_pool_indices[i], p] for p < seq_lens[i]. */
+int bsgl_gather_kv_indices(const int32_t* req_to_token, int64_t page_table_stride,
+                           const int64_t* req_pool_indices, const int32_t* kv_indptr, int batch,
+                           int32_t* kv_indices, void* stream);
+
+/* Number of floats the split-KV partial buffers need: part_o has 2*n_ctas slots of
+ * heads_per_group*group_size*head_dim floats, part_lse 2*n_ctas slots of heads_per_group*group_size. */
+int bsgl_partial_sizes(int n_ctas, int n_q_heads, int n_kv_heads, int head_dim,
+                       int64_t* part_o_floats, int64_t* part_lse_floats);
+
+/* K2/K2b.  Paged GQA attention of one q row per "row" over KV tokens
+ * idx_base[row_idx_off[row] + 0 .. row_kv_len[row]).  Persistent grid of n_ctas CTAs; each CTA
+ * owns an equal contiguous range of 16-token tiles of the flattened (row, head-group) space, so
+ * long and ragged contexts split across CTAs.  Sequences that fall entirely inside one CTA are
+ * written to `out` directly; the others leave normalised partials + base-2 LSE in
+ * part_o/part_lse for bsgl_merge_partials. */
+int bsgl_paged_attention(const void* q, const void* k_slab, const void* v_slab,
+                         const int32_t* idx_base, const int64_t* row_idx_off,
+                         const int32_t* row_kv_len, const int32_t* plan_hdr,
+                         const int32_t* tile_indptr, const int32_t* cta_first_seq,
+                         int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
+                         float sm_scale, int dtype, void* out,
+                         float* part_o, float* part_lse, int n_ctas, void* stream);
+
+/* K2c.  LSE merge of the partials of every sequence that was split; rows with no KV tokens
+ * get zeros.  Must follow bsgl_paged_attention on the same stream with the same plan. */
+int bsgl_merge_partials(const float* part_o, const float* part_lse, const int32_t* plan_hdr,
+                        const int32_t* tile_indptr, int n_rows, int n_q_heads, int n_kv_heads,
+                        int head_dim, int dtype, void* out, void* stream);
+
+/* K3.  Ragged extend attention (radix-cache prefix + new tokens) on tcgen05/TMEM tensor cores.
+ * q rows are packed in request order (qo_indptr); request i's row r sees KV columns
+ * 0..prefix_lens[i]+r of req_to_token[req_pool_indices[i], :seq_lens[i]]. */
+int bsgl_extend_attention(const void* q, const void* k_slab, const void* v_slab,
+                          const int32_t* req_to_token, int64_t page_table_stride,
+                          const int64_t* req_pool_indices, const int64_t* seq_lens,
+                          const int64_t* prefix_lens, const int32_t* qo_indptr,
+                          int batch, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim,
+                          float sm_scale, int dtype, void* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BSGL_B200_H_ */

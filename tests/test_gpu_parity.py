@@ -1,0 +1,211 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the golden fixtures the
+reference produced and against the oracle on seeded inputs.
+
+Tolerances (BASELINE.json north_star): bf16/fp16 outputs max-abs-err <= 2e-2 versus the fp32
+reference; KV-slot / index work bit-exact.
+"""
+import sys
+
+import pytest
+import torch
+
+from oracle import paged_attention_oracle as O
+from tests.helpers import golden_names, load_golden, make_paged_case, slab_checksum
+
+pytestmark = pytest.mark.gpu
+
+TOL = 2e-2          # bf16 output vs fp32 oracle (north_star)
+SPLIT_TOL = 1e-3    # same inputs, different split counts -- on fp32-normalised outputs
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from baby_sglang_b200 import ops as _ops
+    return _ops
+
+
+def _dev(t):
+    return None if t is None else t.cuda()
+
+
+def _run_backend(ops, c, dtype=torch.bfloat16, n_ctas=None, store=True):
+    """kv_store + attention through ops on the case `c` (CPU tensors).  Returns (out, k_slab, v_slab)."""
+    k_slab = c.k_slab.to(dtype).cuda().contiguous()
+    v_slab = c.v_slab.to(dtype).cuda().contiguous()
+    r2t = c.req_to_token.cuda()
+    qkv = c.qkv.to(dtype).cuda()
+    T = qkv.shape[0]
+    q, k, v = qkv.split([c.Hq * c.D, c.Hkv * c.D, c.Hkv * c.D], dim=-1)
+    q = q.contiguous().view(T, c.Hq, c.D)
+    k = k.contiguous().view(T, c.Hkv, c.D)
+    v = v.view(T, c.Hkv, c.D)                    # strided view
+    if store:
+        ops.kv_store(k_slab, v_slab, c.out_cache_loc.cuda(), k, v)
+    if c.is_prefill:
+        md = ops.build_extend_metadata(r2t, c.req_pool_indices.cuda(), c.seq_lens.cuda(), c.prefix_lens.cuda(),
+                                       T, c.Hkv, n_ctas=n_ctas)
+    else:
+        md = ops.build_decode_metadata(r2t, c.req_pool_indices.cuda(), c.seq_lens.cuda(), c.Hkv, n_ctas=n_ctas)
+    out = ops.paged_attention(q, k_slab, v_slab, r2t, md.plan, c.D ** -0.5)
+    torch.cuda.synchronize()
+    return out, k_slab, v_slab, md
+
+
+def _golden_as_case(g):
+    g.k_slab, g.v_slab = g.k_slab0, g.v_slab0
+    return g
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_golden_fixture(ops, name):
+    g = _golden_as_case(load_golden(name))
+    out, k_slab, v_slab, md = _run_backend(ops, g)
+    # K1: bit-exact against the rows the reference wrote, nothing else touched
+    loc = g.out_cache_loc.long()
+    assert torch.equal(k_slab.cpu()[loc].view(torch.int16), g.k_rows1.view(torch.int16))
+    assert torch.equal(v_slab.cpu()[loc].view(torch.int16), g.v_rows1.view(torch.int16))
+    assert slab_checksum(k_slab) == g.k_slab1_sum
+    assert slab_checksum(v_slab) == g.v_slab1_sum
+    # K4: positions / extended_lens bit-exact with the reference's factories
+    assert torch.equal(md.positions.cpu(), g.positions)
+    if g.is_prefill:
+        assert torch.equal(md.extended_lens.cpu(), g.extended_lens)
+    # attention: bf16 out vs the reference's fp32 out
+    assert out.shape == g.out.shape and out.dtype == torch.bfloat16
+    err = (out.float().cpu() - g.out).abs().max().item()
+    assert err <= TOL, err
+
+
+DECODE_CASES = [
+    # (Hq, Hkv, D, seq_lens)
+    (12, 2, 128, [1, 2, 15, 16, 17, 31, 32, 33, 255, 256, 257]),
+    (28, 4, 128, [4096, 3, 777, 2048]),
+    (40, 8, 128, [513, 1200, 64]),
+    (14, 2, 64, [100, 1000, 5]),
+    (5, 1, 128, [300, 17]),              # one KV head (32B under TP8)
+    (8, 8, 128, [90, 91]),               # MHA
+    (16, 2, 128, [1025, 130]),           # G = 8
+]
+
+
+@pytest.mark.parametrize("Hq,Hkv,D,seq_lens", DECODE_CASES)
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_decode_vs_oracle(ops, Hq, Hkv, D, seq_lens, dtype):
+    c = make_paged_case(B=len(seq_lens), Hq=Hq, Hkv=Hkv, D=D, seq_lens=seq_lens, seed=len(seq_lens) * 7 + Hq,
+                        dtype=dtype)
+    out, k_slab, v_slab, _ = _run_backend(ops, c, dtype=dtype)
+    ks, vs = c.k_slab.float().clone(), c.v_slab.float().clone()
+    ref = O.backend_forward(c.q.float(), c.k.float(), c.v.float(), ks, vs, c.req_to_token, c.req_pool_indices,
+                            c.seq_lens, c.out_cache_loc, False)
+    assert torch.equal(k_slab.cpu(), ks.to(dtype)) and torch.equal(v_slab.cpu(), vs.to(dtype))
+    err = (out.float().cpu() - ref).abs().max().item()
+    assert err <= TOL, err
+
+
+EXTEND_CASES = [
+    (12, 2, 128, [40, 9, 130], [0, 0, 0], None),
+    (28, 4, 128, [300, 64, 33, 20], [256, 0, 33, 19], None),
+    (14, 2, 64, [77, 200], [70, 100], None),
+    (40, 8, 128, [96, 100, 70], [64, 64, 40], 0),        # aliased (shared) prefix slots
+]
+
+
+@pytest.mark.parametrize("Hq,Hkv,D,seq_lens,prefix_lens,alias", EXTEND_CASES)
+def test_extend_vs_oracle(ops, Hq, Hkv, D, seq_lens, prefix_lens, alias):
+    c = make_paged_case(B=len(seq_lens), Hq=Hq, Hkv=Hkv, D=D, seq_lens=seq_lens, prefix_lens=prefix_lens,
+                        seed=Hq + D, alias_prefix_of=alias)
+    out, k_slab, v_slab, md = _run_backend(ops, c)
+    ks, vs = c.k_slab.float().clone(), c.v_slab.float().clone()
+    ref = O.backend_forward(c.q.float(), c.k.float(), c.v.float(), ks, vs, c.req_to_token, c.req_pool_indices,
+                            c.seq_lens, c.out_cache_loc, True, c.prefix_lens, c.extended_lens)
+    assert torch.equal(k_slab.cpu(), ks.to(torch.bfloat16))
+    assert out.shape == ref.shape
+    err = (out.float().cpu() - ref).abs().max().item()
+    assert err <= TOL, err
+    omd = O.build_metadata(c.req_to_token, c.req_pool_indices, c.seq_lens, c.prefix_lens)
+    assert torch.equal(md.positions.cpu(), omd.positions)
+    assert torch.equal(md.extended_lens.cpu(), omd.extended_lens)
+    assert torch.equal(md.qo_indptr.cpu(), omd.qo_indptr)
+    assert torch.equal(md.kv_indptr.cpu(), omd.kv_indptr)
+
+
+def test_split_count_invariance(ops):
+    """Same batch under 1, 2, 5, 37 and 148 CTAs: the LSE merge must not change the answer."""
+    c = make_paged_case(B=3, Hq=28, Hkv=4, D=128, seq_lens=[3000, 500, 1234], seed=5)
+    outs = []
+    for n in (1, 2, 5, 37, 148):
+        out, *_ = _run_backend(ops, c, n_ctas=n)
+        outs.append(out.float().cpu())
+    ref = O.decode_attention(c.q.float(), *_stored(c), c.req_to_token, c.req_pool_indices, c.seq_lens)
+    for o in outs:
+        assert (o - ref).abs().max().item() <= TOL
+    for o in outs[1:]:
+        # outputs are rounded to bf16 (ulp 2^-8 relative), so compare at bf16 resolution of |x|<=4
+        assert (o - outs[0]).abs().max().item() <= 2 ** -6
+
+
+def _stored(c):
+    ks, vs = c.k_slab.float().clone(), c.v_slab.float().clone()
+    O.kv_store(ks, vs, c.out_cache_loc, c.k.float(), c.v.float())
+    return ks, vs
+
+
+@pytest.mark.parametrize("nhg_heads", [1, 2, 4, 8])
+@pytest.mark.parametrize("n_ctas", [1, 7, 148])
+def test_decode_metadata_bit_exact(ops, nhg_heads, n_ctas):
+    g = torch.Generator().manual_seed(n_ctas + nhg_heads)
+    B = 300
+    seq = torch.randint(1, 5000, (B,), generator=g)
+    C = 5000
+    r2t = torch.zeros(B + 5, C, dtype=torch.int32)
+    rpi = torch.randperm(B + 5, generator=g)[:B]
+    md = ops.build_decode_metadata(r2t.cuda(), rpi.cuda(), seq.cuda(), nhg_heads, n_ctas=n_ctas)
+    torch.cuda.synchronize()
+    omd = O.build_metadata(r2t, rpi, seq, None)
+    assert torch.equal(md.positions.cpu(), omd.positions)
+    assert torch.equal(md.kv_indptr.cpu(), omd.kv_indptr)
+    assert torch.equal(md.qo_indptr.cpu(), omd.qo_indptr)
+    assert torch.equal(md.plan.row_kv_len.cpu(), seq.to(torch.int32))
+    assert torch.equal(md.plan.row_idx_off.cpu(), rpi * C)
+    nhg = nhg_heads // ops.heads_per_group(nhg_heads)
+    hdr = md.plan.plan_hdr.cpu().tolist()
+    n_eff = hdr[1]
+    tile_indptr, begins, first = O.split_plan(seq.tolist(), nhg, 16, n_eff)
+    assert hdr[0] == tile_indptr[-1] and hdr[2] == B * nhg
+    assert n_eff == max(1, min(n_ctas, tile_indptr[-1] // 4))
+    assert md.plan.tile_indptr.cpu().tolist() == tile_indptr
+    assert md.plan.cta_first_seq.cpu().tolist()[: n_eff + 1] == first
+
+
+def test_kv_indices_gather(ops):
+    c = make_paged_case(B=5, Hq=4, Hkv=2, D=64, seq_lens=[5, 1, 300, 17, 64], seed=3)
+    md = ops.build_decode_metadata(c.req_to_token.cuda(), c.req_pool_indices.cuda(), c.seq_lens.cuda(), 2)
+    got = ops.gather_kv_indices(c.req_to_token.cuda(), c.req_pool_indices.cuda(), md.kv_indptr, int(c.seq_lens.sum()))
+    want = O.build_metadata(c.req_to_token, c.req_pool_indices, c.seq_lens, None).kv_indices
+    assert torch.equal(got.cpu(), want)
+
+
+def test_kv_store_casts_and_strides(ops):
+    torch.manual_seed(0)
+    S, H, D, T = 50, 2, 128, 9
+    for src_dt, dst_dt in [(torch.float32, torch.bfloat16), (torch.float16, torch.bfloat16),
+                           (torch.bfloat16, torch.float16), (torch.float32, torch.float16)]:
+        k_slab = torch.zeros(S + 1, H, D, dtype=dst_dt, device="cuda")
+        v_slab = torch.zeros(S + 1, H, D, dtype=dst_dt, device="cuda")
+        fused = torch.randn(T, 3 * H * D, device="cuda").to(src_dt)
+        k = fused[:, H * D:2 * H * D].view(T, H, D)        # both strided
+        v = fused[:, 2 * H * D:].view(T, H, D)
+        loc = (torch.randperm(S)[:T] + 1).to(torch.int32).cuda()
+        ops.kv_store(k_slab, v_slab, loc, k, v)
+        torch.cuda.synchronize()
+        assert torch.equal(k_slab[loc.long()], k.to(dst_dt))
+        assert torch.equal(v_slab[loc.long()], v.to(dst_dt))
+        assert k_slab[0].abs().sum().item() == 0
+
+
+def test_cpu_tensors_are_refused(ops):
+    from baby_sglang_b200._lib import BsglError
+    with pytest.raises(BsglError):
+        ops.kv_store(torch.zeros(3, 1, 64, dtype=torch.bfloat16), torch.zeros(3, 1, 64, dtype=torch.bfloat16),
+                     torch.tensor([1], dtype=torch.int32), torch.zeros(1, 1, 64, dtype=torch.bfloat16),
+                     torch.zeros(1, 1, 64, dtype=torch.bfloat16))
