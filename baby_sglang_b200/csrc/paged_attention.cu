@@ -57,6 +57,8 @@ struct Cfg {
   static constexpr int CPR = ROW_BYTES / 16;               // 16-byte chunks per row
   static constexpr int RSTEP = kProducerThreads / CPR;      // rows covered by one pass of the producers
   static constexpr int NR = kTile / RSTEP;                  // rows per producer thread per tile
+  static constexpr int PD_RAW = 16 / NR;                    // page-table prefetch distance in tiles
+  static constexpr int PD = PD_RAW < 2 ? 2 : (PD_RAW > 8 ? 8 : PD_RAW);
   static_assert(CPR <= kProducerThreads && kProducerThreads % CPR == 0 && kTile % RSTEP == 0 && NR >= 1,
                 "row width does not map onto the producer threads");
   static constexpr int DP = D + 4;                        // scratch row pitch in floats
@@ -146,31 +148,68 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
 
     if (warp >= kConsumerWarps) {
       // ================================================================ producer warps
+      // Two cursors walk the same (item, tile) sequence: `pf` loads page-table entries PD tiles
+      // ahead into a register ring, `is` waits for a free stage and issues the row gathers.  The
+      // distance hides the dependent idx -> row-address latency even when stages are short
+      // (narrow rows), and it carries across item boundaries.
       const int p = threadIdx.x - kConsumerWarps * 32;
       const int col = p % C::CPR;             // this thread's 16-byte column of every row it copies
       const int r0 = p / C::CPR;              // first row; then every RSTEP-th
       const uint32_t dst0 = stages_u32 + r0 * C::ROW_PITCH + col * 16;
-      for (int ii = 0; ii < n_items; ++ii) {
-        const Item it = items[ii];
-        if (!it.valid) continue;
-        const int ntile = (it.tok_end - it.tok_begin + kTile - 1) / kTile;
-        const int32_t* idxp = idx_base + it.idx_off;
-        const int64_t head_off = (int64_t)it.hg * HPB * D + col * 8;
-        const T* kb = k_slab + head_off;
-        const T* vb = v_slab + head_off;
-        const int last_tok = it.tok_end - 1;   // never read the page table past the sequence
-        int idx_nxt[C::NR];
+      constexpr int PD = C::PD;
+
+      struct Cursor {
+        const int32_t* idxp;
+        int ii, ti, ntile, tok0, last_tok, hg;
+      };
+      auto load_item = [&](Cursor& c) {
+        while (c.ii < n_items && !items[c.ii].valid) ++c.ii;
+        if (c.ii < n_items) {
+          const Item& it = items[c.ii];
+          c.ti = 0;
+          c.ntile = (it.tok_end - it.tok_begin + kTile - 1) / kTile;
+          c.tok0 = it.tok_begin + r0;
+          c.last_tok = it.tok_end - 1;      // never read the page table past the sequence
+          c.idxp = idx_base + it.idx_off;
+          c.hg = it.hg;
+        }
+      };
+      auto advance = [&](Cursor& c) {
+        ++c.ti;
+        c.tok0 += kTile;
+        if (c.ti == c.ntile) {
+          ++c.ii;
+          load_item(c);
+        }
+      };
+      Cursor pf;
+      pf.ii = 0;
+      load_item(pf);
+      Cursor is = pf;
+      int ring[PD][C::NR];
 #pragma unroll
-        for (int i = 0; i < C::NR; ++i) idx_nxt[i] = __ldg(idxp + min(it.tok_begin + r0 + i * C::RSTEP, last_tok));
-        for (int ti = 0; ti < ntile; ++ti) {
+      for (int u = 0; u < PD; ++u) {
+        if (pf.ii < n_items) {
+#pragma unroll
+          for (int i = 0; i < C::NR; ++i) ring[u][i] = __ldg(pf.idxp + min(pf.tok0 + i * C::RSTEP, pf.last_tok));
+          advance(pf);
+        }
+      }
+      while (is.ii < n_items) {
+#pragma unroll
+        for (int u = 0; u < PD; ++u) {
+          if (is.ii >= n_items) break;
           int idx_cur[C::NR];
 #pragma unroll
-          for (int i = 0; i < C::NR; ++i) idx_cur[i] = idx_nxt[i];
-          if (ti + 1 < ntile) {
-            const int tok0 = it.tok_begin + (ti + 1) * kTile + r0;
+          for (int i = 0; i < C::NR; ++i) idx_cur[i] = ring[u][i];
+          if (pf.ii < n_items) {
 #pragma unroll
-            for (int i = 0; i < C::NR; ++i) idx_nxt[i] = __ldg(idxp + min(tok0 + i * C::RSTEP, last_tok));
+            for (int i = 0; i < C::NR; ++i) ring[u][i] = __ldg(pf.idxp + min(pf.tok0 + i * C::RSTEP, pf.last_tok));
+            advance(pf);
           }
+          const int64_t head_off = (int64_t)is.hg * HPB * D + col * 8;
+          const T* kb = k_slab + head_off;
+          const T* vb = v_slab + head_off;
           const uint32_t st = stage_ctr % NST;
           const uint32_t ph = (stage_ctr / NST) & 1;
           mbar_wait(empty_bar0 + 8 * st, ph ^ 1);
@@ -183,6 +222,7 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
           }
           cp_async_mbar_arrive(full_bar0 + 8 * st);
           ++stage_ctr;
+          advance(is);
         }
       }
     } else {

@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--layers", type=int, default=2)
     ap.add_argument("--n-ctas", type=int, default=0)
+    ap.add_argument("--sequential", action="store_true", help="unfragmented page table (slots in order)")
     a = ap.parse_args()
     Hq, Hkv, D = GEOM[a.geom]
     dev = torch.device("cuda")
@@ -32,6 +33,8 @@ def main():
     C = int(seq.max().item()) + 64
     S = int(seq.sum().item()) + 1024
     perm = torch.randperm(S, generator=g, device=dev).to(torch.int32) + 1
+    if a.sequential:
+        perm = torch.arange(1, S + 1, device=dev, dtype=torch.int32)
     r2t = torch.zeros(a.batch, C, dtype=torch.int32, device=dev)
     off = 0
     for i, n in enumerate(seq.tolist()):
@@ -58,7 +61,7 @@ def main():
     tot = int(seq.sum().item())
     bytes_ = tot * Hkv * D * 2 * 2 + 4 * tot + 2 * a.batch * Hq * D * 2
     med = ms[len(ms) // 2]
-    print(json.dumps({"geom": a.geom, "batch": a.batch, "ctx": a.ctx, "ragged": a.ragged, "ms_med": med,
+    print(json.dumps({"geom": a.geom, "batch": a.batch, "ctx": a.ctx, "ragged": a.ragged, "sequential": a.sequential, "ms_med": med,
                       "ms_min": ms[0], "GBps_med": bytes_ / med / 1e6, "GBps_best": bytes_ / ms[0] / 1e6,
                       "frac_of_6524.6": bytes_ / med / 1e6 / 6524.6, "bytes": bytes_,
                       "plan_hdr": md.plan.plan_hdr.tolist()}))
