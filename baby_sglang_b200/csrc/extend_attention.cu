@@ -1,0 +1,447 @@
+// K3  ragged extend attention on tcgen05 tensor cores with TMEM accumulators (sm_100a).
+//
+// Replaces the reference's per-request prefill loop (attn_backend.py:34-110): page-table slice
+// (:54-57), K/V gather of prefix + new tokens (:58-59), GQA repeat_interleave (:61-66), dense
+// additive mask `col > prefix + row` (:74-92), SDPA (:94-101), cat (:110).
+//
+// Work item = (request, KV head, q chunk).  The G q heads that share a KV head are packed into the
+// M dimension: packed row m = token * G + head, 256 packed rows per chunk = two 128-row tiles
+// (A and B) that share one stream of K/V tiles, so every gathered KV row feeds 2 x 128 MMA rows.
+//
+//   producers (3 warps)  gather Q once, then K_j / V_j tiles of 128 KV tokens through the page
+//                        table with 16-byte cp.async into 128B-swizzled UMMA operand layout
+//                        (invalid tokens are zero-filled), 2 stages each; completion is published
+//                        with wait_group + fence.proxy.async + mbarrier arrive.
+//   MMA warp (1 thread)  S_X = Q_X . K_j^T   (tcgen05.mma SS, M128 N128 K16 x D/16, fp32 in TMEM)
+//                        O_X += P_X . V_j    (tcgen05.mma TS: P read from TMEM, V MN-major from smem)
+//                        issue order S_A S_B | PV_A S_A' PV_B S_B' | ... so one tile's softmax
+//                        overlaps the other tile's MMAs; tcgen05.commit signals the mbarriers.
+//   softmax (2 x 4 warps) one thread per row: tcgen05.ld the S row, mask `col <= prefix + token`,
+//                        online softmax in base 2 with lazy rescaling of O (only when the running
+//                        max grows by > 2^8), P written back over S as packed 16-bit pairs
+//                        (tcgen05.st), final O / l -> out.
+//
+// TMEM columns: S_A [0,128) S_B [128,256) O_A [256,256+D) O_B [256+D,256+2D); P_X aliases S_X.
+// Tensor-bound: flops = 4 * Hq * D * sum_i ext_i * (prefix_i + (ext_i + 1) / 2).
+#include "tcgen05.cuh"
+
+namespace bsgl {
+
+constexpr int kExtSoftmaxWarps = 8;
+constexpr int kExtMmaWarp = 8;
+constexpr int kExtProducerWarps = 3;
+constexpr int kExtProducerThreads = kExtProducerWarps * 32;
+constexpr int kExtThreads = (kExtSoftmaxWarps + 1 + kExtProducerWarps) * 32;   // 384
+constexpr int kExtRows = 256;        // packed q rows per chunk (2 MMA tiles)
+constexpr int kExtKvTile = 128;      // KV tokens per tile
+constexpr float kRescaleThreshold = 8.f;   // log2 units
+
+template <int D>
+struct ExtCfg {
+  static constexpr int NH = D / 64;                      // 128-byte column blocks per row
+  static constexpr int HALF_BYTES = 128 * 128;           // [128 rows x 128 B]
+  static constexpr int TILE_BYTES = NH * HALF_BYTES;     // one 128-row operand tile
+  static constexpr int KV_STAGES = D == 128 ? 2 : 4;
+  static constexpr int Q_OFF = 0;
+  static constexpr int K_OFF = 2 * TILE_BYTES;
+  static constexpr int V_OFF = K_OFF + KV_STAGES * TILE_BYTES;
+  static constexpr int BAR_OFF = V_OFF + KV_STAGES * TILE_BYTES;
+  static constexpr int N_BARS = 1 + 4 * KV_STAGES + 4;   // q_full, k/v full/empty, s_full[2], p_full[2]
+  static constexpr int MISC_OFF = BAR_OFF + N_BARS * 8;
+  static constexpr int SMEM_BYTES = MISC_OFF + 64 + 1024;   // + alignment slack
+  static constexpr int TMEM_COLS = 512;
+  static constexpr int O_COL = 256;
+  static constexpr int CPR = D / 8;                      // 16-byte chunks per row
+  static constexpr int RSTEP = kExtProducerThreads / CPR;
+  static constexpr int NR = (128 + RSTEP - 1) / RSTEP;   // rows per producer thread per 128-row tile
+};
+
+struct ExtItem {
+  int req, chunk, found, pad;
+};
+
+template <typename T, int D>
+__global__ void __launch_bounds__(kExtThreads, 1)
+extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, const T* __restrict__ v_slab,
+                        const int32_t* __restrict__ req_to_token, int64_t pt_stride,
+                        const int64_t* __restrict__ req_pool_indices, const int64_t* __restrict__ prefix_lens,
+                        const int32_t* __restrict__ qo_indptr, int batch, int n_q_heads, int n_kv_heads,
+                        float scale_log2, T* __restrict__ out) {
+  using C = ExtCfg<D>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int G = n_q_heads / n_kv_heads;
+  const int TQ = kExtRows / G;                // tokens per chunk
+  const int h = blockIdx.y;                   // KV head
+
+  // ---- which (request, chunk) is this CTA?  chunk counts are ceil(ext_i / TQ); warp 0 scans them.
+  ExtItem* item = reinterpret_cast<ExtItem*>(smem + C::MISC_OFF + 16);
+  if (warp == 0) {
+    const int target = blockIdx.x;
+    int base = 0, found = 0;
+    for (int i0 = 0; i0 < batch && !found; i0 += 32) {
+      const int i = i0 + lane;
+      const int cnt = i < batch ? (qo_indptr[i + 1] - qo_indptr[i] + TQ - 1) / TQ : 0;
+      int incl = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+      }
+      const int lo = base + incl - cnt;
+      const bool hit = target >= lo && target < lo + cnt;
+      if (hit) {
+        item->req = i;
+        item->chunk = target - lo;
+      }
+      found = __any_sync(0xffffffffu, hit);
+      base += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane == 0) item->found = found;
+  }
+  __syncthreads();
+  if (!item->found) return;
+  const int req = item->req;
+  const int q_begin = qo_indptr[req];
+  const int ext = qo_indptr[req + 1] - q_begin;
+  const int prefix = (int)prefix_lens[req];
+  const int t0 = item->chunk * TQ;                       // first token of the chunk inside the extend
+  const int n_tok = min(TQ, ext - t0);
+  const int kv_end = prefix + t0 + n_tok;                // KV tokens the last row of the chunk sees
+  const int nkv = (kv_end + kExtKvTile - 1) / kExtKvTile;
+
+  // ---- barriers, TMEM
+  const uint32_t bar0 = smem_base + C::BAR_OFF;
+  constexpr int KVS = C::KV_STAGES;
+  const uint32_t q_full = bar0;
+  const uint32_t k_full = bar0 + 8, k_empty = k_full + 8 * KVS, v_full = k_empty + 8 * KVS,
+                 v_empty = v_full + 8 * KVS, s_full = v_empty + 8 * KVS, p_full = s_full + 16;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::MISC_OFF);
+  if (threadIdx.x == 0) {
+    mbar_init(q_full, kExtProducerThreads);
+    for (int s = 0; s < KVS; ++s) {
+      mbar_init(k_full + 8 * s, kExtProducerThreads);
+      mbar_init(v_full + 8 * s, kExtProducerThreads);
+      mbar_init(k_empty + 8 * s, 1);
+      mbar_init(v_empty + 8 * s, 1);
+    }
+    for (int x = 0; x < 2; ++x) {
+      mbar_init(s_full + 8 * x, 1);
+      mbar_init(p_full + 8 * x, 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == kExtMmaWarp) {
+    tc::tmem_alloc(smem_u32(tmem_slot), C::TMEM_COLS);
+    tc::tmem_relinquish();
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  const uint32_t q_smem = smem_base + C::Q_OFF, k_smem = smem_base + C::K_OFF, v_smem = smem_base + C::V_OFF;
+
+  if (warp < kExtSoftmaxWarps) {
+    // ============================================================ softmax: one thread per row
+    tc::setmaxnreg_inc<208>();   // 2 x 128 x 208 + 128 x 88 = 384 x 168 registers
+    const int x = warp >> 2;                               // tile A / B
+    const int row = (warp & 3) * 32 + lane;                // TMEM lane
+    const int m = x * 128 + row;                           // packed row in the chunk
+    const int tok = m / G;
+    const int head = m - tok * G;
+    const bool valid = tok < n_tok && m < TQ * G;
+    const int limit = valid ? prefix + t0 + tok : -1;      // last visible KV column
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t s_addr = tmem + lane_base + x * 128;
+    const uint32_t o_addr = tmem + lane_base + C::O_COL + x * D;
+    float m_used = -INFINITY, l = 0.f;
+
+    for (int j = 0; j < nkv; ++j) {
+      mbar_wait_guarded(s_full + 8 * x, j & 1);
+      tc::fence_after_sync();
+      uint32_t s[4][32];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tc::ld32(s_addr + c * 32, s[c]);
+      tc::wait_ld();
+      const int nvalid = limit - j * kExtKvTile + 1;       // visible columns of this tile
+      if (nvalid < kExtKvTile) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (c * 32 + i >= nvalid) s[c][i] = 0xff800000u;   // -inf
+      }
+      float mx = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+#pragma unroll
+        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(s[c][i]));
+      const float m_new = fmaxf(m_used, mx * scale_log2);
+      const bool grow = (m_new - m_used) > kRescaleThreshold;   // false for NaN (-inf - -inf)
+      if (__any_sync(0xffffffffu, grow)) {
+        const float alpha = (m_new == -INFINITY) ? 1.f : fast_exp2(m_used - m_new);
+        l *= alpha;
+        m_used = m_new;
+        if (j > 0) {   // PV_X(j-1) completed before S_X(j) was produced (in-order tensor pipe)
+#pragma unroll
+          for (int c = 0; c < D / 32; ++c) {
+            uint32_t o[32];
+            tc::ld32(o_addr + c * 32, o);
+            tc::wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tc::st32(o_addr + c * 32, o);
+          }
+        }
+      }
+      const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used;
+      float sum = 0.f;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t p[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const int e = c * 64 + 2 * i;
+          const float p0 = fast_exp2(fmaf(__uint_as_float(s[e >> 5][e & 31]), scale_log2, neg_m));
+          const float p1 = fast_exp2(fmaf(__uint_as_float(s[(e + 1) >> 5][(e + 1) & 31]), scale_log2, neg_m));
+          sum += p0 + p1;
+          p[i] = pack2<T>(p0, p1);
+        }
+        tc::st32(s_addr + c * 32, p);
+      }
+      l += sum;
+      tc::wait_st();
+      tc::fence_before_sync();
+      mbar_arrive(p_full + 8 * x);
+    }
+    // ---- epilogue: O / l -> out[token, head, :]
+    mbar_wait_guarded(s_full + 8 * x, nkv & 1);
+    tc::fence_after_sync();
+    const float inv = (valid && l > 0.f) ? 1.f / l : 0.f;
+    T* orow = out + ((int64_t)(q_begin + t0 + tok) * n_q_heads + (int64_t)h * G + head) * D;
+#pragma unroll
+    for (int c = 0; c < D / 32; ++c) {
+      uint32_t o[32];
+      tc::ld32(o_addr + c * 32, o);
+      tc::wait_ld();
+      if (valid) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 8) {
+          uint4 pk;
+          pk.x = pack2<T>(__uint_as_float(o[i]) * inv, __uint_as_float(o[i + 1]) * inv);
+          pk.y = pack2<T>(__uint_as_float(o[i + 2]) * inv, __uint_as_float(o[i + 3]) * inv);
+          pk.z = pack2<T>(__uint_as_float(o[i + 4]) * inv, __uint_as_float(o[i + 5]) * inv);
+          pk.w = pack2<T>(__uint_as_float(o[i + 6]) * inv, __uint_as_float(o[i + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + c * 32 + i) = pk;
+        }
+      }
+    }
+    tc::fence_before_sync();
+  } else if (warp == kExtMmaWarp) {
+    // ============================================================ MMA issuer (one thread)
+    tc::setmaxnreg_dec<88>();
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = tc::instr_desc<T>(128, kExtKvTile, 0, 0);
+      constexpr uint32_t idesc_pv = tc::instr_desc<T>(128, D, 0, 1);
+      auto issue_s = [&](int x, int st) {
+        const uint32_t qa = q_smem + x * C::TILE_BYTES, kb = k_smem + st * C::TILE_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * C::HALF_BYTES + (kk & 3) * 32;
+          tc::mma_ss(tmem + x * 128, tc::smem_desc_sw128(qa + off, 16, 1024),
+                     tc::smem_desc_sw128(kb + off, 16, 1024), idesc_s, kk > 0);
+        }
+      };
+      auto issue_pv = [&](int x, int st, bool acc) {
+        const uint32_t vb = v_smem + st * C::TILE_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < kExtKvTile / 16; ++kk) {
+          // 16 KV tokens per step = two 8-row groups (SBO 1024 B); 64-wide D blocks LBO apart
+          tc::mma_ts(tmem + C::O_COL + x * D, tmem + x * 128 + kk * 8,
+                     tc::smem_desc_sw128(vb + kk * 2048, C::HALF_BYTES, 1024), idesc_pv, acc || kk > 0);
+        }
+      };
+      mbar_wait_guarded(q_full, 0);
+      mbar_wait_guarded(k_full, 0);
+      tc::fence_after_sync();
+      issue_s(0, 0);
+      tc::commit(s_full);
+      issue_s(1, 0);
+      tc::commit(s_full + 8);
+      tc::commit(k_empty);
+      for (int j = 0; j < nkv; ++j) {
+        const int st = j % KVS;
+        const uint32_t ph = (j / KVS) & 1;
+        mbar_wait_guarded(v_full + 8 * st, ph);
+        for (int x = 0; x < 2; ++x) {
+          mbar_wait_guarded(p_full + 8 * x, j & 1);
+          tc::fence_after_sync();
+          issue_pv(x, st, j > 0);
+          if (x == 1) tc::commit(v_empty + 8 * st);
+          if (j + 1 < nkv) {
+            const int st1 = (j + 1) % KVS;
+            if (x == 0) {
+              mbar_wait_guarded(k_full + 8 * st1, ((j + 1) / KVS) & 1);
+              tc::fence_after_sync();
+            }
+            issue_s(x, st1);
+            tc::commit(s_full + 8 * x);
+            if (x == 1) tc::commit(k_empty + 8 * st1);
+          } else {
+            tc::commit(s_full + 8 * x);     // O_X complete
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ============================================================ producers: gather Q, K_j, V_j
+    tc::setmaxnreg_dec<88>();
+    const int p = threadIdx.x - (kExtMmaWarp + 1) * 32;
+    const int c16 = p % C::CPR;                            // 16-byte chunk of the row
+    const int r0 = p / C::CPR;
+    const uint32_t col_off = (c16 >> 3) * C::HALF_BYTES;
+    const int cc = c16 & 7;
+    auto dst_of = [&](int r) { return col_off + (uint32_t)r * 128u + (uint32_t)((cc ^ (r & 7)) << 4); };
+
+    // Q: packed row m = token * G + head; the G heads of a token are contiguous in q.
+    for (int mrow = r0; mrow < kExtRows; mrow += C::RSTEP) {
+      const int tok = mrow / G;
+      const int head = mrow - tok * G;
+      const bool ok = tok < n_tok && mrow < TQ * G;
+      const T* src = q + ((int64_t)(q_begin + t0 + (ok ? tok : 0)) * n_q_heads + (int64_t)h * G + (ok ? head : 0)) * D +
+                     c16 * 8;
+      cp_async16_zfill(q_smem + (mrow >> 7) * C::TILE_BYTES + dst_of(mrow & 127), src, ok ? 16u : 0u);
+    }
+    cp_async_commit();
+
+    const int32_t* idxp = req_to_token + req_pool_indices[req] * pt_stride;
+    const int64_t slab_row = (int64_t)n_kv_heads * D;
+    const T* kb = k_slab + (int64_t)h * D + c16 * 8;
+    const T* vb = v_slab + (int64_t)h * D + c16 * 8;
+    uint32_t prev_bar = q_full;
+    for (int j = 0; j < nkv; ++j) {
+      const int st = j % KVS;
+      const uint32_t ph = (j / KVS) & 1;
+      // page-table entries of this tile (-1 = past the chunk's last visible token: zero-fill);
+      // their latency hides behind the wait for a free stage
+      int idx[C::NR];
+#pragma unroll
+      for (int i = 0; i < C::NR; ++i) {
+        const int r = r0 + i * C::RSTEP;
+        const int t = j * kExtKvTile + r;
+        idx[i] = (r < kExtKvTile && t < kv_end) ? __ldg(idxp + t) : -1;
+      }
+      // K_j
+      mbar_wait_guarded(k_empty + 8 * st, ph ^ 1);
+#pragma unroll
+      for (int i = 0; i < C::NR; ++i) {
+        const int r = r0 + i * C::RSTEP;
+        if (r < kExtKvTile) {
+          const bool ok = idx[i] >= 0;
+          cp_async16_zfill(k_smem + st * C::TILE_BYTES + dst_of(r), kb + (ok ? idx[i] : 0) * slab_row, ok ? 16u : 0u);
+        }
+      }
+      cp_async_commit();
+      cp_async_wait<1>();             // the previous group (Q or V_{j-1}) has landed
+      fence_proxy_async_smem();
+      mbar_arrive(prev_bar);
+      // V_j
+      mbar_wait_guarded(v_empty + 8 * st, ph ^ 1);
+#pragma unroll
+      for (int i = 0; i < C::NR; ++i) {
+        const int r = r0 + i * C::RSTEP;
+        if (r < kExtKvTile) {
+          const bool ok = idx[i] >= 0;
+          cp_async16_zfill(v_smem + st * C::TILE_BYTES + dst_of(r), vb + (ok ? idx[i] : 0) * slab_row, ok ? 16u : 0u);
+        }
+      }
+      cp_async_commit();
+      cp_async_wait<1>();             // K_j has landed
+      fence_proxy_async_smem();
+      mbar_arrive(k_full + 8 * st);
+      prev_bar = v_full + 8 * st;
+    }
+    cp_async_wait<0>();
+    fence_proxy_async_smem();
+    mbar_arrive(prev_bar);
+  }
+
+  // ---- teardown: every TMEM read is done before the allocation is released
+  __syncthreads();
+  if (warp == kExtMmaWarp) {
+    tc::fence_after_sync();
+    tc::tmem_dealloc(tmem, C::TMEM_COLS);
+  }
+}
+
+}  // namespace bsgl
+
+// ------------------------------------------------------------------------------------ launcher
+namespace bsgl {
+
+template <typename T, int D>
+static int launch_extend(const void* q, const void* k_slab, const void* v_slab, const int32_t* req_to_token,
+                         int64_t pt_stride, const int64_t* req_pool_indices, const int64_t* prefix_lens,
+                         const int32_t* qo_indptr, int batch, int64_t n_tokens, int n_q_heads, int n_kv_heads,
+                         float sm_scale, void* out, cudaStream_t stream) {
+  using C = ExtCfg<D>;
+  auto kern = extend_attention_kernel<T, D>;
+  static thread_local int configured_dev = -1;
+  int dev = 0;
+  BSGL_CUDA_TRY(cudaGetDevice(&dev));
+  if (configured_dev != dev) {
+    BSGL_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    configured_dev = dev;
+  }
+  const int G = n_q_heads / n_kv_heads;
+  const int TQ = kExtRows / G;
+  // sum_i ceil(ext_i / TQ) <= floor(T / TQ) + batch; surplus CTAs exit before touching TMEM
+  const int64_t max_chunks = n_tokens / TQ + batch;
+  BSGL_REQUIRE(max_chunks < (1ll << 31), "bsgl_extend_attention: too many q chunks");
+  dim3 grid((unsigned)max_chunks, (unsigned)n_kv_heads);
+  const float scale_log2 = sm_scale * 1.4426950408889634f;
+  kern<<<grid, kExtThreads, C::SMEM_BYTES, stream>>>((const T*)q, (const T*)k_slab, (const T*)v_slab, req_to_token,
+                                                     pt_stride, req_pool_indices, prefix_lens, qo_indptr, batch,
+                                                     n_q_heads, n_kv_heads, scale_log2, (T*)out);
+  return check_launch("extend_attention_kernel");
+}
+
+}  // namespace bsgl
+
+extern "C" int bsgl_extend_attention(const void* q, const void* k_slab, const void* v_slab,
+                                     const int32_t* req_to_token, int64_t page_table_stride,
+                                     const int64_t* req_pool_indices, const int64_t* seq_lens,
+                                     const int64_t* prefix_lens, const int32_t* qo_indptr, int batch,
+                                     int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim, float sm_scale,
+                                     int dtype, void* out, void* stream) {
+  using namespace bsgl;
+  (void)seq_lens;   // seq = prefix + ext; ext comes from qo_indptr
+  BSGL_REQUIRE(batch >= 0 && n_tokens >= 0, "bsgl_extend_attention: negative sizes");
+  if (batch == 0 || n_tokens == 0) return BSGL_OK;
+  BSGL_REQUIRE(q && k_slab && v_slab && req_to_token && req_pool_indices && prefix_lens && qo_indptr && out,
+               "bsgl_extend_attention: null pointer");
+  BSGL_REQUIRE(n_kv_heads > 0 && n_q_heads % n_kv_heads == 0, "bsgl_extend_attention: n_q_heads %% n_kv_heads != 0");
+  const int G = n_q_heads / n_kv_heads;
+  BSGL_REQUIRE(G <= 128, "bsgl_extend_attention: GQA group size %d > 128 is not supported", G);
+  BSGL_REQUIRE(n_kv_heads <= 65535, "bsgl_extend_attention: too many KV heads");
+  BSGL_REQUIRE(head_dim == 64 || head_dim == 128, "bsgl_extend_attention: head_dim %d not in {64,128}", head_dim);
+  BSGL_REQUIRE(dtype == BSGL_BF16 || dtype == BSGL_F16, "bsgl_extend_attention: dtype must be bf16 or fp16");
+  BSGL_REQUIRE(((uintptr_t)q % 16 == 0) && ((uintptr_t)k_slab % 16 == 0) && ((uintptr_t)v_slab % 16 == 0) &&
+                   ((uintptr_t)out % 16 == 0),
+               "bsgl_extend_attention: pointers must be 16-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+#define BSGL_EXT(T, D)                                                                                              \
+  return launch_extend<T, D>(q, k_slab, v_slab, req_to_token, page_table_stride, req_pool_indices, prefix_lens,    \
+                             qo_indptr, batch, n_tokens, n_q_heads, n_kv_heads, sm_scale, out, s)
+  if (dtype == BSGL_BF16) {
+    if (head_dim == 128) BSGL_EXT(__nv_bfloat16, 128);
+    BSGL_EXT(__nv_bfloat16, 64);
+  }
+  if (head_dim == 128) BSGL_EXT(__half, 128);
+  BSGL_EXT(__half, 64);
+#undef BSGL_EXT
+}

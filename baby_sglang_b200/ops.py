@@ -8,6 +8,7 @@ here computes: without a CUDA device and the built library these functions raise
 from __future__ import annotations
 
 import ctypes
+import os
 from dataclasses import dataclass
 from typing import Optional, Tuple
 
@@ -171,13 +172,15 @@ def build_decode_metadata(req_to_token: torch.Tensor, req_pool_indices: torch.Te
 def build_extend_metadata(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
                           seq_lens: torch.Tensor, prefix_lens: torch.Tensor, n_tokens: int,
                           n_kv_heads: int, n_ctas: Optional[int] = None,
-                          row_plan: bool = True) -> BatchMetadata:
+                          row_plan: Optional[bool] = None) -> BatchMetadata:
     """Device-side replacement of create_prefill_batch's host loop (forward_batch.py:36-45) and of
     the per-request `.item()` chain in `_prefill_attention` (attn_backend.py:43-57).  `n_tokens`
     (= q rows) is known on the host: it is `input_ids.shape[0]`."""
     dev = _require_cuda(req_to_token, req_pool_indices, seq_lens, prefix_lens)
     B = int(req_pool_indices.shape[0])
     T = int(n_tokens)
+    if row_plan is None:   # the per-token split-KV plan is only needed by the row-wise path
+        row_plan = extend_mode(T, B) == "rowwise"
     nhg = int(n_kv_heads) // heads_per_group(n_kv_heads)
     n_ctas = n_ctas or sm_count(dev)
     rpi, sl, pl = _as_i64(req_pool_indices), _as_i64(seq_lens), _as_i64(prefix_lens)
@@ -271,14 +274,69 @@ def paged_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor,
 
 
 # --------------------------------------------------------------------------------------- K3
+#: extends with at most this many new tokens per request on average run row-wise on the split-KV
+#: kernel (a 256-row tensor-core chunk would be mostly padding); everything else runs on tcgen05.
+ROWWISE_MAX_AVG_EXTEND = 4
+
+
+def extend_mode(n_tokens: int, batch: int) -> str:
+    forced = os.environ.get("BSGL_EXTEND_MODE", "")
+    if forced in ("tcgen05", "rowwise"):
+        return forced
+    return "rowwise" if n_tokens <= ROWWISE_MAX_AVG_EXTEND * max(batch, 1) else "tcgen05"
+
+
+def extend_attention_tc(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor, req_to_token: torch.Tensor,
+                        req_pool_indices: torch.Tensor, seq_lens: torch.Tensor, prefix_lens: torch.Tensor,
+                        qo_indptr: torch.Tensor, sm_scale: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """K3: ragged extend attention on tcgen05/TMEM (reference `_prefill_attention`,
+    attn_backend.py:34-110).  q rows are packed in request order (`qo_indptr`); request i's row r
+    sees KV columns 0..prefix_i + r of its page-table row."""
+    dev = _require_cuda(q, k_slab, v_slab, req_to_token, req_pool_indices, seq_lens, prefix_lens, qo_indptr)
+    if q.dim() != 3:
+        raise _lib.BsglError(f"q must be [tokens, Hq, D], got {tuple(q.shape)}")
+    T, Hq, D = q.shape
+    Hkv = int(k_slab.shape[1])
+    if int(k_slab.shape[2]) != D or Hq % Hkv != 0:
+        raise _lib.BsglError("KV slab geometry does not match q")
+    if q.dtype != k_slab.dtype or q.dtype != v_slab.dtype:
+        raise _lib.BsglError(f"q dtype {q.dtype} != KV slab dtype {k_slab.dtype}")
+    if req_to_token.dtype != torch.int32 or qo_indptr.dtype != torch.int32:
+        raise _lib.BsglError("page table and qo_indptr must be int32")
+    if not q.is_contiguous():
+        q = q.contiguous()
+    if out is None:
+        out = torch.empty((T, Hq * D), dtype=q.dtype, device=dev)
+    B = int(req_pool_indices.shape[0])
+    if T == 0 or B == 0:
+        return out
+    rpi, sl, pl = _as_i64(req_pool_indices), _as_i64(seq_lens), _as_i64(prefix_lens)
+    rc = _lib.load().bsgl_extend_attention(
+        q.data_ptr(), k_slab.data_ptr(), v_slab.data_ptr(), req_to_token.data_ptr(), req_to_token.stride(0),
+        rpi.data_ptr(), sl.data_ptr(), pl.data_ptr(), qo_indptr.data_ptr(), B, T, Hq, Hkv, D, float(sm_scale),
+        dtype_code(q.dtype), out.data_ptr(), _stream())
+    _lib.check(rc, "bsgl_extend_attention")
+    _count()
+    return out
+
+
 def extend_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor, forward_batch,
-                     md: BatchMetadata, sm_scale: float) -> torch.Tensor:
+                     md: BatchMetadata, sm_scale: float, mode: Optional[str] = None) -> torch.Tensor:
     """Ragged extend (reference `_prefill_attention`, attn_backend.py:34-110).
 
-    Row-wise formulation: q token t of request i is a sequence of prefix_i + r + 1 KV tokens over
-    request i's page-table row, which is exactly the causal-within-extend mask `col <= prefix+row`
-    (attn_backend.py:83-85); it runs on the split-KV kernel with the per-row plan K4 built.
-    """
-    if md.plan is None:
-        raise _lib.BsglError("extend metadata was built without a row plan")
-    return paged_attention(q, k_slab, v_slab, forward_batch.req_to_token_pool.req_to_token, md.plan, sm_scale)
+    "tcgen05": K3, the tensor-core kernel.  "rowwise" (tiny extends): q token t of request i is a
+    sequence of prefix_i + r + 1 KV tokens over request i's page-table row, which is exactly the
+    mask `col <= prefix+row` (attn_backend.py:83-85); it runs on the split-KV kernel (K2) with the
+    per-row plan K4 builds."""
+    r2t = forward_batch.req_to_token_pool.req_to_token
+    B = int(forward_batch.req_pool_indices.shape[0])
+    mode = mode or extend_mode(int(q.shape[0]), B)
+    if mode == "tcgen05":
+        return extend_attention_tc(q, k_slab, v_slab, r2t, forward_batch.req_pool_indices, forward_batch.seq_lens,
+                                   forward_batch.prefix_lens, md.qo_indptr, sm_scale)
+    if md.plan is None:   # metadata was built for the tensor-core path: add the row plan now
+        full = build_extend_metadata(r2t, forward_batch.req_pool_indices, forward_batch.seq_lens,
+                                     forward_batch.prefix_lens, int(q.shape[0]), int(k_slab.shape[1]),
+                                     row_plan=True)
+        md.plan = full.plan
+    return paged_attention(q, k_slab, v_slab, r2t, md.plan, sm_scale)

@@ -28,8 +28,9 @@ def _dev(t):
     return None if t is None else t.cuda()
 
 
-def _run_backend(ops, c, dtype=torch.bfloat16, n_ctas=None, store=True):
-    """kv_store + attention through ops on the case `c` (CPU tensors).  Returns (out, k_slab, v_slab)."""
+def _run_backend(ops, c, dtype=torch.bfloat16, n_ctas=None, store=True, extend_mode="tcgen05"):
+    """kv_store + attention through ops on the case `c` (CPU tensors).  Returns (out, k_slab, v_slab, md).
+    Extend cases run on K3 (`extend_mode="tcgen05"`) or row-wise on K2 (`"rowwise"`)."""
     k_slab = c.k_slab.to(dtype).cuda().contiguous()
     v_slab = c.v_slab.to(dtype).cuda().contiguous()
     r2t = c.req_to_token.cuda()
@@ -43,10 +44,15 @@ def _run_backend(ops, c, dtype=torch.bfloat16, n_ctas=None, store=True):
         ops.kv_store(k_slab, v_slab, c.out_cache_loc.cuda(), k, v)
     if c.is_prefill:
         md = ops.build_extend_metadata(r2t, c.req_pool_indices.cuda(), c.seq_lens.cuda(), c.prefix_lens.cuda(),
-                                       T, c.Hkv, n_ctas=n_ctas)
+                                       T, c.Hkv, n_ctas=n_ctas, row_plan=(extend_mode == "rowwise"))
+        if extend_mode == "rowwise":
+            out = ops.paged_attention(q, k_slab, v_slab, r2t, md.plan, c.D ** -0.5)
+        else:
+            out = ops.extend_attention_tc(q, k_slab, v_slab, r2t, c.req_pool_indices.cuda(), c.seq_lens.cuda(),
+                                          c.prefix_lens.cuda(), md.qo_indptr, c.D ** -0.5)
     else:
         md = ops.build_decode_metadata(r2t, c.req_pool_indices.cuda(), c.seq_lens.cuda(), c.Hkv, n_ctas=n_ctas)
-    out = ops.paged_attention(q, k_slab, v_slab, r2t, md.plan, c.D ** -0.5)
+        out = ops.paged_attention(q, k_slab, v_slab, r2t, md.plan, c.D ** -0.5)
     torch.cuda.synchronize()
     return out, k_slab, v_slab, md
 
@@ -56,10 +62,13 @@ def _golden_as_case(g):
     return g
 
 
+@pytest.mark.parametrize("extend_mode", ["tcgen05", "rowwise"])
 @pytest.mark.parametrize("name", golden_names())
-def test_golden_fixture(ops, name):
+def test_golden_fixture(ops, name, extend_mode):
     g = _golden_as_case(load_golden(name))
-    out, k_slab, v_slab, md = _run_backend(ops, g)
+    if not g.is_prefill and extend_mode == "rowwise":
+        pytest.skip("decode fixtures have one path")
+    out, k_slab, v_slab, md = _run_backend(ops, g, extend_mode=extend_mode)
     # K1: bit-exact against the rows the reference wrote, nothing else touched
     loc = g.out_cache_loc.long()
     assert torch.equal(k_slab.cpu()[loc].view(torch.int16), g.k_rows1.view(torch.int16))
@@ -103,18 +112,26 @@ def test_decode_vs_oracle(ops, Hq, Hkv, D, seq_lens, dtype):
 
 
 EXTEND_CASES = [
+    # (Hq, Hkv, D, seq_lens, prefix_lens, alias_prefix_of)
     (12, 2, 128, [40, 9, 130], [0, 0, 0], None),
     (28, 4, 128, [300, 64, 33, 20], [256, 0, 33, 19], None),
     (14, 2, 64, [77, 200], [70, 100], None),
     (40, 8, 128, [96, 100, 70], [64, 64, 40], 0),        # aliased (shared) prefix slots
+    (28, 4, 128, [1500, 700, 129], [1000, 0, 128], None),  # many KV tiles, several q chunks
+    (12, 2, 128, [513, 600], [1, 0], None),              # G = 6, 15 q chunks
+    (8, 8, 128, [300, 10], [0, 9], None),                # MHA: one q head per KV head
+    (16, 2, 128, [260, 255], [200, 0], None),            # G = 8
+    (4, 2, 64, [700], [100], None),                      # G = 2, D = 64
+    (5, 1, 128, [400, 3], [399, 0], None),               # one-token extend after a long prefix
 ]
 
 
+@pytest.mark.parametrize("extend_mode", ["tcgen05", "rowwise"])
 @pytest.mark.parametrize("Hq,Hkv,D,seq_lens,prefix_lens,alias", EXTEND_CASES)
-def test_extend_vs_oracle(ops, Hq, Hkv, D, seq_lens, prefix_lens, alias):
+def test_extend_vs_oracle(ops, Hq, Hkv, D, seq_lens, prefix_lens, alias, extend_mode):
     c = make_paged_case(B=len(seq_lens), Hq=Hq, Hkv=Hkv, D=D, seq_lens=seq_lens, prefix_lens=prefix_lens,
                         seed=Hq + D, alias_prefix_of=alias)
-    out, k_slab, v_slab, md = _run_backend(ops, c)
+    out, k_slab, v_slab, md = _run_backend(ops, c, extend_mode=extend_mode)
     ks, vs = c.k_slab.float().clone(), c.v_slab.float().clone()
     ref = O.backend_forward(c.q.float(), c.k.float(), c.v.float(), ks, vs, c.req_to_token, c.req_pool_indices,
                             c.seq_lens, c.out_cache_loc, True, c.prefix_lens, c.extended_lens)
@@ -127,6 +144,39 @@ def test_extend_vs_oracle(ops, Hq, Hkv, D, seq_lens, prefix_lens, alias):
     assert torch.equal(md.extended_lens.cpu(), omd.extended_lens)
     assert torch.equal(md.qo_indptr.cpu(), omd.qo_indptr)
     assert torch.equal(md.kv_indptr.cpu(), omd.kv_indptr)
+
+
+def test_extend_fp16_and_modes_agree(ops):
+    """fp16 through K3, and K3 against the row-wise K2 path on the same inputs."""
+    c = make_paged_case(B=3, Hq=28, Hkv=4, D=128, seq_lens=[640, 200, 77], prefix_lens=[512, 0, 70], seed=21,
+                        dtype=torch.float16)
+    a, *_ = _run_backend(ops, c, dtype=torch.float16, extend_mode="tcgen05")
+    b, *_ = _run_backend(ops, c, dtype=torch.float16, extend_mode="rowwise")
+    ks, vs = c.k_slab.float().clone(), c.v_slab.float().clone()
+    ref = O.backend_forward(c.q.float(), c.k.float(), c.v.float(), ks, vs, c.req_to_token, c.req_pool_indices,
+                            c.seq_lens, c.out_cache_loc, True, c.prefix_lens, c.extended_lens)
+    assert (a.float().cpu() - ref).abs().max().item() <= TOL
+    assert (a.float() - b.float()).abs().max().item() <= 2 ** -6
+
+
+def test_extend_many_requests(ops):
+    """More requests than one scan round of the work-item search (B > 32), ragged, some empty extends."""
+    g = torch.Generator().manual_seed(77)
+    B = 70
+    pre = torch.randint(0, 300, (B,), generator=g).tolist()
+    ext = torch.randint(0, 90, (B,), generator=g).tolist()
+    ext[3] = 0
+    ext[40] = 0
+    seq = [p + e for p, e in zip(pre, ext)]
+    seq = [max(s, 1) for s in seq]
+    pre = [min(p, s) for p, s in zip(pre, seq)]
+    c = make_paged_case(B=B, Hq=12, Hkv=2, D=128, seq_lens=seq, prefix_lens=pre, seed=9)
+    out, *_ = _run_backend(ops, c, extend_mode="tcgen05")
+    ks, vs = c.k_slab.float().clone(), c.v_slab.float().clone()
+    ref = O.backend_forward(c.q.float(), c.k.float(), c.v.float(), ks, vs, c.req_to_token, c.req_pool_indices,
+                            c.seq_lens, c.out_cache_loc, True, c.prefix_lens, c.extended_lens)
+    assert out.shape == ref.shape
+    assert (out.float().cpu() - ref).abs().max().item() <= TOL
 
 
 def test_split_count_invariance(ops):
