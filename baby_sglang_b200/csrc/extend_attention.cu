@@ -10,8 +10,10 @@
 //
 //   producers (3 warps)  gather Q once, then K_j / V_j tiles of 128 KV tokens through the page
 //                        table with 16-byte cp.async into 128B-swizzled UMMA operand layout
-//                        (invalid tokens are zero-filled), 2 stages each; completion is published
-//                        with wait_group + fence.proxy.async + mbarrier arrive.
+//                        (invalid tokens are zero-filled); K and V tiles alternate through one ring
+//                        of 5 x 32 KB slots; completion is published per slot with
+//                        cp.async.mbarrier.arrive, the MMA thread orders the generic and async
+//                        proxies (fence.proxy.async) after waiting and before issuing.
 //   MMA warp (1 thread)  S_X = Q_X . K_j^T   (tcgen05.mma SS, M128 N128 K16 x D/16, fp32 in TMEM)
 //                        O_X += P_X . V_j    (tcgen05.mma TS: P read from TMEM, V MN-major from smem)
 //                        issue order S_A S_B | PV_A S_A' PV_B S_B' | ... so one tile's softmax
@@ -41,14 +43,16 @@ struct ExtCfg {
   static constexpr int NH = D / 64;                      // 128-byte column blocks per row
   static constexpr int HALF_BYTES = 128 * 128;           // [128 rows x 128 B]
   static constexpr int TILE_BYTES = NH * HALF_BYTES;     // one 128-row operand tile
-  static constexpr int KV_STAGES = D == 128 ? 2 : 4;
+  // K and V tiles alternate through ONE ring (K_0 V_0 K_1 V_1 ...): tile u = 2j (K_j) or 2j+1 (V_j)
+  // lives in slot u % RING.  An odd ring size keeps 2.5 KV steps in flight next to the 2 q tiles.
+  static constexpr int RING = D == 128 ? 5 : 8;
   static constexpr int Q_OFF = 0;
-  static constexpr int K_OFF = 2 * TILE_BYTES;
-  static constexpr int V_OFF = K_OFF + KV_STAGES * TILE_BYTES;
-  static constexpr int BAR_OFF = V_OFF + KV_STAGES * TILE_BYTES;
-  static constexpr int N_BARS = 1 + 4 * KV_STAGES + 4;   // q_full, k/v full/empty, s_full[2], p_full[2]
+  static constexpr int RING_OFF = 2 * TILE_BYTES;
+  static constexpr int BAR_OFF = RING_OFF + RING * TILE_BYTES;
+  static constexpr int N_BARS = 1 + 2 * RING + 4;        // q_full, full/empty per slot, s_full[2], p_full[2]
   static constexpr int MISC_OFF = BAR_OFF + N_BARS * 8;
   static constexpr int SMEM_BYTES = MISC_OFF + 64 + 1024;   // + alignment slack
+  static_assert(SMEM_BYTES <= 227 * 1024, "extend kernel shared memory over budget");
   static constexpr int TMEM_COLS = 512;
   static constexpr int O_COL = 256;
   static constexpr int CPR = D / 8;                      // 16-byte chunks per row
@@ -94,7 +98,7 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
       const bool hit = target >= lo && target < lo + cnt;
       if (hit) {
         item->req = i;
-        item->chunk = target - lo;
+        item->chunk = cnt - 1 - (target - lo);   // a request's longest-KV chunk is dispatched first
       }
       found = __any_sync(0xffffffffu, hit);
       base += __shfl_sync(0xffffffffu, incl, 31);
@@ -114,18 +118,15 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
 
   // ---- barriers, TMEM
   const uint32_t bar0 = smem_base + C::BAR_OFF;
-  constexpr int KVS = C::KV_STAGES;
+  constexpr int RING = C::RING;
   const uint32_t q_full = bar0;
-  const uint32_t k_full = bar0 + 8, k_empty = k_full + 8 * KVS, v_full = k_empty + 8 * KVS,
-                 v_empty = v_full + 8 * KVS, s_full = v_empty + 8 * KVS, p_full = s_full + 16;
+  const uint32_t full0 = bar0 + 8, empty0 = full0 + 8 * RING, s_full = empty0 + 8 * RING, p_full = s_full + 16;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::MISC_OFF);
   if (threadIdx.x == 0) {
-    mbar_init(q_full, kExtProducerThreads);
-    for (int s = 0; s < KVS; ++s) {
-      mbar_init(k_full + 8 * s, kExtProducerThreads);
-      mbar_init(v_full + 8 * s, kExtProducerThreads);
-      mbar_init(k_empty + 8 * s, 1);
-      mbar_init(v_empty + 8 * s, 1);
+    mbar_init(q_full, kExtProducerThreads);       // one cp.async-completion arrive per producer thread
+    for (int s = 0; s < RING; ++s) {
+      mbar_init(full0 + 8 * s, kExtProducerThreads);
+      mbar_init(empty0 + 8 * s, 1);               // tcgen05.commit
     }
     for (int x = 0; x < 2; ++x) {
       mbar_init(s_full + 8 * x, 1);
@@ -142,7 +143,7 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
   tc::fence_after_sync();
   const uint32_t tmem = *tmem_slot;
 
-  const uint32_t q_smem = smem_base + C::Q_OFF, k_smem = smem_base + C::K_OFF, v_smem = smem_base + C::V_OFF;
+  const uint32_t q_smem = smem_base + C::Q_OFF, ring_smem = smem_base + C::RING_OFF;
 
   if (warp < kExtSoftmaxWarps) {
     // ============================================================ softmax: one thread per row
@@ -246,8 +247,15 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
     if (lane == 0) {
       constexpr uint32_t idesc_s = tc::instr_desc<T>(128, kExtKvTile, 0, 0);
       constexpr uint32_t idesc_pv = tc::instr_desc<T>(128, D, 0, 1);
-      auto issue_s = [&](int x, int st) {
-        const uint32_t qa = q_smem + x * C::TILE_BYTES, kb = k_smem + st * C::TILE_BYTES;
+      // Operand tiles were written by cp.async (generic proxy) and are read by the tensor core
+      // (async proxy): wait for the copies, then order the two proxies before issuing.
+      auto wait_tile = [&](int u) {
+        mbar_wait_guarded(full0 + 8 * (u % RING), (u / RING) & 1);
+        fence_proxy_async_smem();
+        tc::fence_after_sync();
+      };
+      auto issue_s = [&](int x, int u) {
+        const uint32_t qa = q_smem + x * C::TILE_BYTES, kb = ring_smem + (u % RING) * C::TILE_BYTES;
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t off = (kk >> 2) * C::HALF_BYTES + (kk & 3) * 32;
@@ -255,8 +263,8 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
                      tc::smem_desc_sw128(kb + off, 16, 1024), idesc_s, kk > 0);
         }
       };
-      auto issue_pv = [&](int x, int st, bool acc) {
-        const uint32_t vb = v_smem + st * C::TILE_BYTES;
+      auto issue_pv = [&](int x, int u, bool acc) {
+        const uint32_t vb = ring_smem + (u % RING) * C::TILE_BYTES;
 #pragma unroll
         for (int kk = 0; kk < kExtKvTile / 16; ++kk) {
           // 16 KV tokens per step = two 8-row groups (SBO 1024 B); 64-wide D blocks LBO apart
@@ -265,31 +273,25 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
         }
       };
       mbar_wait_guarded(q_full, 0);
-      mbar_wait_guarded(k_full, 0);
-      tc::fence_after_sync();
+      wait_tile(0);
       issue_s(0, 0);
       tc::commit(s_full);
       issue_s(1, 0);
       tc::commit(s_full + 8);
-      tc::commit(k_empty);
+      tc::commit(empty0);
       for (int j = 0; j < nkv; ++j) {
-        const int st = j % KVS;
-        const uint32_t ph = (j / KVS) & 1;
-        mbar_wait_guarded(v_full + 8 * st, ph);
+        const int uv = 2 * j + 1, uk = 2 * j + 2;     // V_j, K_{j+1}
+        wait_tile(uv);
         for (int x = 0; x < 2; ++x) {
           mbar_wait_guarded(p_full + 8 * x, j & 1);
           tc::fence_after_sync();
-          issue_pv(x, st, j > 0);
-          if (x == 1) tc::commit(v_empty + 8 * st);
+          issue_pv(x, uv, j > 0);
+          if (x == 1) tc::commit(empty0 + 8 * (uv % RING));
           if (j + 1 < nkv) {
-            const int st1 = (j + 1) % KVS;
-            if (x == 0) {
-              mbar_wait_guarded(k_full + 8 * st1, ((j + 1) / KVS) & 1);
-              tc::fence_after_sync();
-            }
-            issue_s(x, st1);
+            if (x == 0) wait_tile(uk);
+            issue_s(x, uk);
             tc::commit(s_full + 8 * x);
-            if (x == 1) tc::commit(k_empty + 8 * st1);
+            if (x == 1) tc::commit(empty0 + 8 * (uk % RING));
           } else {
             tc::commit(s_full + 8 * x);     // O_X complete
           }
@@ -316,18 +318,15 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
                      c16 * 8;
       cp_async16_zfill(q_smem + (mrow >> 7) * C::TILE_BYTES + dst_of(mrow & 127), src, ok ? 16u : 0u);
     }
-    cp_async_commit();
+    cp_async_mbar_arrive(q_full);
 
     const int32_t* idxp = req_to_token + req_pool_indices[req] * pt_stride;
     const int64_t slab_row = (int64_t)n_kv_heads * D;
     const T* kb = k_slab + (int64_t)h * D + c16 * 8;
     const T* vb = v_slab + (int64_t)h * D + c16 * 8;
-    uint32_t prev_bar = q_full;
     for (int j = 0; j < nkv; ++j) {
-      const int st = j % KVS;
-      const uint32_t ph = (j / KVS) & 1;
       // page-table entries of this tile (-1 = past the chunk's last visible token: zero-fill);
-      // their latency hides behind the wait for a free stage
+      // their latency hides behind the wait for a free slot
       int idx[C::NR];
 #pragma unroll
       for (int i = 0; i < C::NR; ++i) {
@@ -335,39 +334,25 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
         const int t = j * kExtKvTile + r;
         idx[i] = (r < kExtKvTile && t < kv_end) ? __ldg(idxp + t) : -1;
       }
-      // K_j
-      mbar_wait_guarded(k_empty + 8 * st, ph ^ 1);
 #pragma unroll
-      for (int i = 0; i < C::NR; ++i) {
-        const int r = r0 + i * C::RSTEP;
-        if (r < kExtKvTile) {
-          const bool ok = idx[i] >= 0;
-          cp_async16_zfill(k_smem + st * C::TILE_BYTES + dst_of(r), kb + (ok ? idx[i] : 0) * slab_row, ok ? 16u : 0u);
-        }
-      }
-      cp_async_commit();
-      cp_async_wait<1>();             // the previous group (Q or V_{j-1}) has landed
-      fence_proxy_async_smem();
-      mbar_arrive(prev_bar);
-      // V_j
-      mbar_wait_guarded(v_empty + 8 * st, ph ^ 1);
+      for (int kv = 0; kv < 2; ++kv) {               // K_j then V_j, same rows
+        const int u = 2 * j + kv;
+        const int slot = u % RING;
+        mbar_wait_guarded(empty0 + 8 * slot, ((u / RING) & 1) ^ 1);
+        const T* base = kv == 0 ? kb : vb;
+        const uint32_t dst = ring_smem + slot * C::TILE_BYTES;
 #pragma unroll
-      for (int i = 0; i < C::NR; ++i) {
-        const int r = r0 + i * C::RSTEP;
-        if (r < kExtKvTile) {
-          const bool ok = idx[i] >= 0;
-          cp_async16_zfill(v_smem + st * C::TILE_BYTES + dst_of(r), vb + (ok ? idx[i] : 0) * slab_row, ok ? 16u : 0u);
+        for (int i = 0; i < C::NR; ++i) {
+          const int r = r0 + i * C::RSTEP;
+          if (r < kExtKvTile) {
+            const bool ok = idx[i] >= 0;
+            cp_async16_zfill(dst + dst_of(r), base + (ok ? idx[i] : 0) * slab_row, ok ? 16u : 0u);
+          }
         }
+        cp_async_mbar_arrive(full0 + 8 * slot);      // arrives when this thread's copies have landed
       }
-      cp_async_commit();
-      cp_async_wait<1>();             // K_j has landed
-      fence_proxy_async_smem();
-      mbar_arrive(k_full + 8 * st);
-      prev_bar = v_full + 8 * st;
     }
-    cp_async_wait<0>();
-    fence_proxy_async_smem();
-    mbar_arrive(prev_bar);
+    cp_async_wait_all();                             // nothing of this CTA is in flight at exit
   }
 
   // ---- teardown: every TMEM read is done before the allocation is released
