@@ -1,0 +1,196 @@
+"""Drop-in for the reference's `tp_runtime` module (reference tp_runtime.py:10-51) plus the wiring the
+reference leaves as a roadmap item (it defines the four helpers but never calls them, README.md:50).
+
+Same four public names and semantics:
+
+    init_tp() -> (rank, world_size, tp_group)      env RANK / WORLD_SIZE / LOCAL_RANK          tp_runtime.py:10-25
+    tp_all_reduce_sum(x, tp_group)                 in-place SUM all-reduce, returns x           :28-33
+    tp_all_gather(x, tp_group)                     all-gather + cat(dim=0)                      :36-43
+    tp_broadcast(x, src, tp_group)                 in-place broadcast                           :46-51
+
+The attention path shards only along its natural, exchange-free axes:
+
+  * KV-head tensor parallelism when `num_kv_heads % world == 0`: rank r owns KV heads
+    [r*Hkv/t, (r+1)*Hkv/t) and their G q heads each.  Page table, slot allocator, radix cache and
+    scheduler are replicated and identical on every rank (the same slot numbers index different head
+    slices), so paged attention itself needs no collective; ONE collective per layer follows it: the SUM
+    all-reduce of the bias-free `o_proj` partial `[T, hidden]` (qwen2.py:166,195) over NCCL / NVLink.
+    `shard_attention_heads(model, ...)` wires this into the reference's UNCHANGED model by slicing the
+    fused QKV / o_proj weights of each attention module in place and hooking `o_proj`.
+  * request-batch data parallelism otherwise: `dp_partition` splits the request list; replicas are
+    independent (no collective in the data path).
+"""
+from __future__ import annotations
+
+import copy
+import os
+from dataclasses import dataclass
+from typing import List, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+__all__ = ["init_tp", "tp_all_reduce_sum", "tp_all_gather", "tp_broadcast", "plan_parallelism", "ParallelPlan",
+           "shard_attention_heads", "kv_pool_config", "dp_partition", "dp_gather_outputs"]
+
+
+# ------------------------------------------------------------------------------------------------------
+# the reference's four helpers
+# ------------------------------------------------------------------------------------------------------
+def init_tp() -> Tuple[int, int, object]:
+    rank = int(os.getenv("RANK", "0"))
+    world_size = int(os.getenv("WORLD_SIZE", "1"))
+    local_rank = int(os.getenv("LOCAL_RANK", "0"))
+    cuda = torch.cuda.is_available()
+    if cuda:
+        torch.cuda.set_device(local_rank)
+    if world_size > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        # NCCL over NVLink/NVSwitch on GPUs (the reference's backend); gloo only exists so the host logic can
+        # be exercised on a machine without GPUs.
+        if cuda:
+            dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
+        else:
+            dist.init_process_group(backend="gloo")
+    tp_group = dist.group.WORLD
+    if dist.is_initialized():
+        rank = dist.get_rank(group=tp_group)
+        world_size = dist.get_world_size(group=tp_group)
+    return rank, world_size, tp_group
+
+
+def _world(tp_group) -> int:
+    return dist.get_world_size(group=tp_group) if dist.is_initialized() else 1
+
+
+def tp_all_reduce_sum(x: torch.Tensor, tp_group) -> torch.Tensor:
+    if _world(tp_group) == 1:
+        return x
+    dist.all_reduce(x, op=dist.ReduceOp.SUM, group=tp_group)
+    return x
+
+
+def tp_all_gather(x: torch.Tensor, tp_group) -> torch.Tensor:
+    world = _world(tp_group)
+    if world == 1:
+        return x
+    out = torch.empty((world * x.shape[0],) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+    dist.all_gather_into_tensor(out, x.contiguous(), group=tp_group)   # == cat(gather_list, dim=0)
+    return out
+
+
+def tp_broadcast(x: torch.Tensor, src: int, tp_group) -> torch.Tensor:
+    if _world(tp_group) == 1:
+        return x
+    dist.broadcast(x, src=src, group=tp_group)
+    return x
+
+
+# ------------------------------------------------------------------------------------------------------
+# which shard applies
+# ------------------------------------------------------------------------------------------------------
+@dataclass(frozen=True)
+class ParallelPlan:
+    mode: str            # "single" | "kv_head_tp" | "request_dp"
+    world_size: int
+    kv_heads_per_rank: int
+    q_heads_per_rank: int
+
+
+def plan_parallelism(num_q_heads: int, num_kv_heads: int, world_size: int) -> ParallelPlan:
+    """KV-head TP where `num_kv_heads >= world` and divisible; request-batch DP otherwise."""
+    if world_size <= 1:
+        return ParallelPlan("single", 1, num_kv_heads, num_q_heads)
+    if num_kv_heads >= world_size and num_kv_heads % world_size == 0:
+        return ParallelPlan("kv_head_tp", world_size, num_kv_heads // world_size, num_q_heads // world_size)
+    return ParallelPlan("request_dp", world_size, num_kv_heads, num_q_heads)
+
+
+# ------------------------------------------------------------------------------------------------------
+# KV-head tensor parallelism on an unchanged model
+# ------------------------------------------------------------------------------------------------------
+def _attention_modules(model: torch.nn.Module):
+    """Every module shaped like the reference's Qwen2Attention (qwen2.py:143-177): a fused `qkv_proj.qkv_proj`
+    linear, a bias-free `o_proj`, an `attn` shim and the head bookkeeping attributes."""
+    for m in model.modules():
+        inner = getattr(getattr(m, "qkv_proj", None), "qkv_proj", None)
+        if isinstance(inner, torch.nn.Linear) and isinstance(getattr(m, "o_proj", None), torch.nn.Linear) \
+                and hasattr(m, "attn") and hasattr(m, "num_kv_heads"):
+            yield m
+
+
+def shard_attention_heads(model: torch.nn.Module, rank: int, world_size: int, tp_group) -> ParallelPlan:
+    """Mutate `model` in place so this rank computes its KV heads only.
+
+    Per attention module: keep rows [q heads of this rank | k heads | v heads] of the fused QKV weight and
+    bias (layout `[Hq*D | Hkv*D | Hkv*D]`, qwen2.py:279-289), keep the matching input columns of `o_proj`,
+    patch `num_heads / num_kv_heads / q_size / kv_size` (qwen2.py:157-161,279-281) and the backend-facing
+    `attn.tp_*_head_num` (qwen2.py:302-304), and all-reduce `o_proj`'s output with a forward hook.  `head_dim`
+    is untouched (the reference derives it from `hidden_size // num_heads` at construction, qwen2.py:159).
+    """
+    mods = list(_attention_modules(model))
+    if not mods:
+        raise ValueError("model has no attention modules of the expected shape")
+    plan = plan_parallelism(mods[0].num_heads, mods[0].num_kv_heads, world_size)
+    if plan.mode != "kv_head_tp":
+        return plan
+    for m in mods:
+        Hq, Hkv, D = m.num_heads, m.num_kv_heads, m.head_dim
+        G = Hq // Hkv
+        kv_lo, kv_hi = rank * plan.kv_heads_per_rank, (rank + 1) * plan.kv_heads_per_rank
+        q_lo, q_hi = kv_lo * G, kv_hi * G
+        lin = m.qkv_proj.qkv_proj
+        rows = torch.cat([torch.arange(q_lo * D, q_hi * D),
+                          Hq * D + torch.arange(kv_lo * D, kv_hi * D),
+                          (Hq + Hkv) * D + torch.arange(kv_lo * D, kv_hi * D)]).to(lin.weight.device)
+        with torch.no_grad():
+            lin.weight = torch.nn.Parameter(lin.weight.index_select(0, rows).contiguous(), requires_grad=False)
+            if lin.bias is not None:
+                lin.bias = torch.nn.Parameter(lin.bias.index_select(0, rows).contiguous(), requires_grad=False)
+            lin.out_features = int(rows.numel())
+            o = m.o_proj
+            o.weight = torch.nn.Parameter(o.weight[:, q_lo * D:q_hi * D].contiguous(), requires_grad=False)
+            o.in_features = (q_hi - q_lo) * D
+        m.num_heads, m.num_kv_heads = q_hi - q_lo, kv_hi - kv_lo
+        m.q_size, m.kv_size = m.num_heads * D, m.num_kv_heads * D
+        for holder in (m.qkv_proj,):
+            if hasattr(holder, "num_heads"):
+                holder.num_heads, holder.num_kv_heads = m.num_heads, m.num_kv_heads
+                holder.q_size, holder.kv_size = m.q_size, m.kv_size
+                holder.total_size = m.q_size + 2 * m.kv_size
+        m.attn.tp_q_head_num, m.attn.tp_k_head_num, m.attn.tp_v_head_num = m.num_heads, m.num_kv_heads, m.num_kv_heads
+        m.o_proj.register_forward_hook(lambda _mod, _inp, out, g=tp_group: tp_all_reduce_sum(out, g))
+    return plan
+
+
+def kv_pool_config(config, plan: ParallelPlan):
+    """Config copy for the (unchanged) scheduler's pool construction: it sizes the KV pool with
+    `num_key_value_heads` and `hidden_size // num_attention_heads` (scheduler.py:50-57), so only the KV-head count
+    shrinks under TP; everything else — and therefore head_dim — stays."""
+    cfg = copy.copy(config)
+    if plan.mode == "kv_head_tp":
+        cfg.num_key_value_heads = plan.kv_heads_per_rank
+    return cfg
+
+
+# ------------------------------------------------------------------------------------------------------
+# request-batch data parallelism
+# ------------------------------------------------------------------------------------------------------
+def dp_partition(n_requests: int, rank: int, world_size: int) -> List[int]:
+    """Round-robin share of request indices for this replica."""
+    return list(range(rank, n_requests, max(world_size, 1)))
+
+
+def dp_gather_outputs(local_outputs: Sequence[Sequence[int]], n_requests: int, rank: int, world_size: int,
+                      tp_group) -> List[List[int]]:
+    """Reassemble per-request token lists from all replicas in the original request order."""
+    if world_size <= 1 or not dist.is_initialized():
+        return [list(o) for o in local_outputs]
+    gathered: List[object] = [None] * world_size
+    dist.all_gather_object(gathered, [list(o) for o in local_outputs], group=tp_group)
+    out: List[List[int]] = [[] for _ in range(n_requests)]
+    for r, part in enumerate(gathered):
+        for j, idx in enumerate(dp_partition(n_requests, r, world_size)):
+            out[idx] = part[j]
+    return out
