@@ -193,12 +193,23 @@ class Stack:
     backend_forward: Callable
 
 
+@dataclass
+class GreedyTrace:
+    ids: List[List[int]]          # tokens fed forward (argmax, or the forced ones)
+    pred: List[List[int]]         # this stack's own argmax at every step
+    top1: List[List[float]]       # top-1 logit value per step
+    margin: List[List[float]]     # top-1 minus top-2 logit per step
+    pools: tuple
+
+
 def greedy_generate(model: HarnessQwen2, stack: Stack, prompts: List[List[int]], max_new_tokens: int, device,
-                    dtype, reuse_prefix: Optional[List[int]] = None, pools=None, max_total_tokens: int = 0):
-    """Prefill all prompts in one extend batch, then `max_new_tokens - 1` decode steps; returns (token ids per
-    request, pools).  With `reuse_prefix` (tokens per request) and the `pools` of an earlier call on the same
-    prompts, the first `reuse_prefix[i]` page-table cells of request i are kept (a radix-cache hit,
-    scheduler.py:423-442) and only the rest of the prompt is extended."""
+                    dtype, reuse_prefix: Optional[List[int]] = None, pools=None, max_total_tokens: int = 0,
+                    forced_ids: Optional[List[List[int]]] = None) -> GreedyTrace:
+    """Prefill all prompts in one extend batch, then `max_new_tokens - 1` decode steps.  With `reuse_prefix`
+    (tokens per request) and the `pools` of an earlier call on the same prompts, the first `reuse_prefix[i]`
+    page-table cells of request i are kept (a radix-cache hit, scheduler.py:423-442) and only the rest of the
+    prompt is extended.  `forced_ids` feeds the given tokens forward instead of this stack's own argmax
+    (teacher forcing), while `pred` still records the argmax."""
     cfg = model.config
     B = len(prompts)
     head_dim = cfg.hidden_size // cfg.num_attention_heads
@@ -231,20 +242,28 @@ def greedy_generate(model: HarnessQwen2, stack: Stack, prompts: List[List[int]],
         prefix_lens=torch.tensor(prefix, dtype=torch.int64, device=device))
     logits = model(fb.input_ids, fb.positions, fb)
     last = torch.cumsum(torch.tensor(ext, device=device), 0) - 1
-    nxt = logits[last].float().argmax(dim=-1)
-    out = [[int(t)] for t in nxt.tolist()]
-    margins = []
-    for _ in range(max_new_tokens - 1):
+    logits = logits[last].float()
+    tr = GreedyTrace([[] for _ in range(B)], [[] for _ in range(B)], [[] for _ in range(B)],
+                     [[] for _ in range(B)], (r2t, kvp, rows))
+
+    def record(lg, step):
+        top2 = lg.topk(2, dim=-1)
+        pred = top2.indices[:, 0]
+        nxt = pred if forced_ids is None else torch.tensor([f[step] for f in forced_ids], device=device)
+        for i in range(B):
+            tr.pred[i].append(int(pred[i]))
+            tr.ids[i].append(int(nxt[i]))
+            tr.top1[i].append(float(top2.values[i, 0]))
+            tr.margin[i].append(float(top2.values[i, 0] - top2.values[i, 1]))
+        return nxt
+
+    nxt = record(logits, 0)
+    for step in range(1, max_new_tokens):
         slots = kvp.alloc(B)
         r2t.req_to_token[rpi, seq] = slots.to(torch.int32)
         seq = seq + 1
         fb = stack.SimplifiedForwardBatch.create_decode_batch(
             input_ids=nxt, req_pool_indices=rpi, seq_lens=seq, out_cache_loc=slots.to(torch.int32),
             req_to_token_pool=r2t, token_to_kv_pool=kvp)
-        logits = model(fb.input_ids, fb.positions, fb).float()
-        top2 = logits.topk(2, dim=-1).values
-        margins.append((top2[:, 0] - top2[:, 1]).min().item())
-        nxt = logits.argmax(dim=-1)
-        for i, t in enumerate(nxt.tolist()):
-            out[i].append(int(t))
-    return out, (r2t, kvp, rows), margins
+        nxt = record(model(fb.input_ids, fb.positions, fb).float(), step)
+    return tr

@@ -86,7 +86,7 @@ def _body_kv_head_tp(tp, rank, world, group):
     prompts = [torch.randint(0, cfg.vocab_size, (n,), generator=g).tolist() for n in (21, 4, 40)]
     full = HarnessQwen2(cfg, st.backend_forward).float().eval()
     deterministic_weights(full)
-    want, _, _ = greedy_generate(full, st, prompts, 12, torch.device("cpu"), torch.float32)
+    want = greedy_generate(full, st, prompts, 12, torch.device("cpu"), torch.float32).ids
 
     sharded = HarnessQwen2(cfg, st.backend_forward).float().eval()
     deterministic_weights(sharded)
@@ -98,9 +98,9 @@ def _body_kv_head_tp(tp, rank, world, group):
     assert at.attn.tp_q_head_num == 2 and at.attn.tp_k_head_num == 1
     pool_cfg = tp.kv_pool_config(cfg, plan)
     assert pool_cfg.num_key_value_heads == 1 and cfg.num_key_value_heads == 2
-    got, pools, _ = greedy_generate(sharded, st, prompts, 12, torch.device("cpu"), torch.float32)
-    assert pools[1].head_num == 1            # per-rank KV pool holds Hkv / t heads
-    assert got == want, f"rank {rank}: TP token ids differ"
+    tr = greedy_generate(sharded, st, prompts, 12, torch.device("cpu"), torch.float32)
+    assert tr.pools[1].head_num == 1         # per-rank KV pool holds Hkv / t heads
+    assert tr.ids == want, f"rank {rank}: TP token ids differ"
 
 
 def _body_dp_plan(tp, rank, world, group):
