@@ -58,6 +58,29 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def traffic_from_profiles(key):
+    """dram bytes per launch of the dominant kernel, from the committed ncu --set full capture (or None)."""
+    path = os.path.join(REPO, "profiles", "r1_traffic.json")
+    try:
+        with open(path) as f:
+            return int(json.load(f)[key]["dram_bytes"])
+    except Exception:
+        return None
+
+
+def tensor_peak():
+    path = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        with open(path) as f:
+            return float(json.load(f)["bf16_tflops"]), "measured burst (MEASURED_PEAKS.json bf16_tflops)"
+    return 1590.0, "fallback (B200_PROFILING.md 1.59 PFLOP/s)"
+
+
+def extend_flops(Hq, D, prefix, ext):
+    """QK^T and PV, unmasked MACs only."""
+    return 4.0 * Hq * D * sum(e * (p + (e + 1) / 2.0) for p, e in zip(prefix, ext))
+
+
 def decode_bytes(sum_seq, B, Hq, Hkv, D, e=2):
     """K+V rows once per KV head + int32 page-table entries + q read + out write."""
     return sum_seq * Hkv * D * 2 * e + 4 * sum_seq + 2 * B * Hq * D * e
@@ -173,17 +196,88 @@ def build_workload(name, device, seed, Hkv_override=None, Hq_override=None):
     return w
 
 
+def measure_extend_c3(device, reps=10):
+    """Config C3: Qwen2.5-7B geometry, B=16, prefix_i ~ U[0,8192] (first two forced to 0 and
+    8192), 512 new tokens each, bf16, fragmented page table; K3 (tcgen05) timed alone with CUDA events.
+    The 151 MB KV working set is re-read across launches from HBM/L2 mix; the kernel is tensor-bound."""
+    from baby_sglang_b200 import ops
+    Hq, Hkv, D, _, _ = GEOMETRY["qwen2.5-7b"]
+    B, ext_len, max_prefix = 16, 512, 8192
+    g = torch.Generator().manual_seed(0)
+    prefix = torch.randint(0, max_prefix + 1, (B,), generator=g)
+    prefix[0], prefix[1] = 0, max_prefix
+    ext = torch.full((B,), ext_len, dtype=torch.int64)
+    seq = prefix + ext
+    C = int(seq.max()) + 64
+    S = int(seq.sum()) + 1024
+    perm = (torch.randperm(S, generator=g) + 1).to(torch.int32)
+    r2t = torch.zeros(B, C, dtype=torch.int32)
+    off = 0
+    for i, n in enumerate(seq.tolist()):
+        r2t[i, :n] = perm[off:off + n]
+        off += n
+    T = int(ext.sum())
+    dt = torch.bfloat16
+    k_slab = torch.randn(S + 1, Hkv, D, device=device, dtype=dt)
+    v_slab = torch.randn(S + 1, Hkv, D, device=device, dtype=dt)
+    q = torch.randn(T, Hq, D, device=device, dtype=dt)
+    r2t, rpi = r2t.to(device), torch.arange(B, device=device)
+    seq_d, pre_d = seq.to(device), prefix.to(device)
+    md = ops.build_extend_metadata(r2t, rpi, seq_d, pre_d, T, Hkv, row_plan=False)
+    out = torch.empty(T, Hq * D, device=device, dtype=dt)
+    for _ in range(3):
+        ops.extend_attention_tc(q, k_slab, v_slab, r2t, rpi, seq_d, pre_d, md.qo_indptr, D ** -0.5, out=out)
+    torch.cuda.synchronize()
+    evs = []
+    for _ in range(reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        ops.extend_attention_tc(q, k_slab, v_slab, r2t, rpi, seq_d, pre_d, md.qo_indptr, D ** -0.5, out=out)
+        b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    ms = statistics.mean(a.elapsed_time(b) for a, b in evs)
+    fl = extend_flops(Hq, D, prefix.tolist(), ext.tolist())
+    peak, src = tensor_peak()
+    ach = fl / ms / 1e9
+    return {"bound": "tensor", "kernel": "extend_attention_kernel (tcgen05/TMEM)", "achieved": round(ach, 1),
+            "peak": peak, "unit": "TFLOP/s", "frac": round(ach / peak, 4), "peak_source": src,
+            "flops_per_launch": fl, "avg_launch_ms": round(ms, 5), "traffic": traffic_from_profiles("extend_c3"),
+            "workload": "qwen2.5-7b extend (config C3): B=16, prefix U[0,8192], 512 new tokens each, bf16"}
+
+
 def run_b200(args, rank, world, device):
     from baby_sglang_b200 import ops
-    w = build_workload(args.workload, device, seed=1234 + rank)
+    model_name = WORKLOADS[args.workload][0]
+    Hq_full, Hkv_full = GEOMETRY[model_name][0], GEOMETRY[model_name][1]
+    # c5: KV-head tensor parallelism (rank r owns Hkv/t KV heads of EVERY request; identical page table on all
+    # ranks; one SUM all-reduce of the o_proj partial per layer).  Everything else: request-batch DP.
+    tp = args.workload == "c5" and world > 1 and Hkv_full % world == 0
+    if tp:
+        w = build_workload(args.workload, device, seed=1234, Hkv_override=Hkv_full // world,
+                           Hq_override=Hq_full // world)
+    else:
+        w = build_workload(args.workload, device, seed=1234 + rank)
     import attn_backend   # drop-in modules (sys.path set by build_workload)
     import forward_batch
+    import tp_runtime
     B, Hq, Hkv, D, L = w["B"], w["Hq"], w["Hkv"], w["D"], w["L"]
     dt = torch.bfloat16
+    with_oproj = args.workload == "c5"
+    tp_group = torch.distributed.group.WORLD if world > 1 else None
+    if with_oproj:   # this rank's column shard of o_proj (bias-free, qwen2.py:166): partial sums are exact
+        w_o = torch.randn(w["hidden"], Hq * D, device=device, dtype=dt) * 0.02
+
+    def after_attention(out):
+        if not with_oproj:
+            return out
+        partial = torch.nn.functional.linear(out, w_o)
+        return tp_runtime.tp_all_reduce_sum(partial, tp_group) if tp else partial
     # per-layer activations of one step, device-resident (for `value`) and pinned host copies (for `e2e`)
     qkv_dev = [torch.randn(B, (Hq + 2 * Hkv) * D, device=device, dtype=dt) for _ in range(L)]
     qkv_host = [t.cpu().pin_memory() for t in qkv_dev]
-    out_host = [torch.empty(B, Hq * D, dtype=dt).pin_memory() for _ in range(L)]
+    out_host = [torch.empty(B, w["hidden"] if args.workload == "c5" else Hq * D, dtype=dt).pin_memory()
+                for _ in range(L)]
     ids_host = torch.zeros(B, dtype=torch.int64).pin_memory()
     rpi_host = w["rpi"].cpu().pin_memory()
     seq_host = w["seq"].cpu().pin_memory()
@@ -204,7 +298,7 @@ def run_b200(args, rank, world, device):
         out = None
         for l in range(L):
             q, k, v = qkv_split_dev[l]
-            out = attn_backend.SimpleAttentionBackend.forward(q, k, v, w["layers"][l], fb, True)
+            out = after_attention(attn_backend.SimpleAttentionBackend.forward(q, k, v, w["layers"][l], fb, True))
         return out
 
     def step_e2e():
@@ -217,7 +311,7 @@ def run_b200(args, rank, world, device):
             req_to_token_pool=w["r2t_pool"], token_to_kv_pool=w["kv_pool"])
         for l in range(L):
             q, k, v = split(qkv_host[l].to(device, non_blocking=True))
-            out = attn_backend.SimpleAttentionBackend.forward(q, k, v, w["layers"][l], fb, True)
+            out = after_attention(attn_backend.SimpleAttentionBackend.forward(q, k, v, w["layers"][l], fb, True))
             out_host[l].copy_(out, non_blocking=True)
         torch.cuda.current_stream().synchronize()   # the caller reads out_host
         return out_host[L - 1]
@@ -279,8 +373,29 @@ def run_b200(args, rank, world, device):
     peak, peak_src = peaks()
     achieved = k_bytes / k_ms / 1e6
 
+    allreduce = None
+    if tp:
+        buf = torch.randn(B, w["hidden"], device=device, dtype=dt)
+        for _ in range(5):
+            tp_runtime.tp_all_reduce_sum(buf, tp_group)
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n_ar = 20
+        a.record()
+        for _ in range(n_ar):
+            tp_runtime.tp_all_reduce_sum(buf, tp_group)
+        b.record()
+        barrier()
+        t = torch.tensor([a.elapsed_time(b) / n_ar], device=device)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        ar_ms = float(t.item())
+        nbytes = buf.numel() * buf.element_size()
+        allreduce = {"bytes": nbytes, "avg_ms": round(ar_ms, 5),
+                     "busbw_GBps": round(2 * (world - 1) / world * nbytes / ar_ms / 1e6, 1),
+                     "backend": "NCCL over NVLink/NVSwitch (torch.distributed all_reduce SUM)"}
     if rank != 0:
         return
+    extend = measure_extend_c3(device) if world == 1 else None    # the tensor-bound kernel of the path (K3)
     cpu = cpu_baseline(args.workload, seconds=12.0)
     value = world * step_bytes / ms_step / 1e6
     e2e_v = world * step_bytes / ms_e2e / 1e6
@@ -289,14 +404,18 @@ def run_b200(args, rank, world, device):
     line = {
         "metric": METRIC if args.workload == "ns" else f"paged decode attn HBM GB/s, workload {args.workload}",
         "value": round(value, 1), "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"{w['model']} paged GQA decode ({Hq}q/{Hkv}kv, D={D}), batch {B}/GPU, "
+        "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong" if tp else "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"{w['model']} paged GQA decode ({Hq}q/{Hkv}kv{' per rank' if tp else ''}, D={D}), "
+                               f"batch {B}{'' if tp else '/GPU'}, "
                                f"ctx {WORKLOADS[args.workload][2]}..{WORKLOADS[args.workload][3]}, page_size 1, "
                                f"{L} layers/step, fragmented page table",
-                   "parallelism": "request-batch DP (no collective)" if world > 1 else "single GPU",
+                   "parallelism": (f"KV-head TP x{world}: o_proj partial + NCCL all-reduce per layer" if tp else
+                                   "request-batch DP (no collective)" if world > 1 else "single GPU"),
                    "l2": f"inputs > L2: {k_bytes / 1e9:.2f} GB of KV per layer, {L} distinct layers per step",
-                   "step": "K4 metadata + per layer (K1 kv_store, K2 paged attention, K2c merge)"},
+                   "step": "K4 metadata + per layer (K1 kv_store, K2 paged attention, K2c merge"
+                           + (", o_proj shard GEMM" + (", all-reduce" if tp else "") if with_oproj else "") + ")"},
+        "allreduce": allreduce,
         "decode_tok_per_s_attention_path": round(world * B / (ms_step / 1e3), 1),
         "e2e": {"value": round(e2e_v, 1), "unit": "GB/s", "ms_per_step": round(ms_e2e, 4),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -305,7 +424,10 @@ def run_b200(args, rank, world, device):
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "paged_attention_kernel", "achieved": round(achieved, 1),
                      "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "peak_source": peak_src,
-                     "bytes_per_launch": k_bytes, "avg_launch_ms": round(k_ms, 5), "traffic": args.traffic},
+                     "bytes_per_launch": k_bytes, "avg_launch_ms": round(k_ms, 5),
+                     "traffic": args.traffic if args.traffic is not None else
+                     (traffic_from_profiles(args.workload) if world == 1 else None)},
+        "extend_roofline": extend,
         "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)
