@@ -25,6 +25,8 @@
 //
 // TMEM columns: S_A [0,128) S_B [128,256) O_A [256,256+D) O_B [256+D,256+2D); P_X aliases S_X.
 // Tensor-bound: flops = 4 * Hq * D * sum_i ext_i * (prefix_i + (ext_i + 1) / 2).
+#include <cstdlib>
+
 #include "tcgen05.cuh"
 
 namespace bsgl {
@@ -64,7 +66,7 @@ struct ExtItem {
   int req, chunk, found, pad;
 };
 
-template <typename T, int D>
+template <typename T, int D, int EXPMODE>
 __global__ void __launch_bounds__(kExtThreads, 1)
 extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, const T* __restrict__ v_slab,
                         const int32_t* __restrict__ req_to_token, int64_t pt_stride,
@@ -175,11 +177,17 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
           for (int i = 0; i < 32; ++i)
             if (c * 32 + i >= nvalid) s[c][i] = 0xff800000u;   // -inf
       }
-      float mx = -INFINITY;
+      float mxs[8];
 #pragma unroll
-      for (int c = 0; c < 4; ++c)
+      for (int i = 0; i < 8; ++i)
+        mxs[i] = fmaxf(fmaxf(__uint_as_float(s[0][i]), __uint_as_float(s[1][i])),
+                       fmaxf(__uint_as_float(s[2][i]), __uint_as_float(s[3][i])));
 #pragma unroll
-        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(s[c][i]));
+      for (int i = 8; i < 32; ++i)
+        mxs[i & 7] = fmaxf(mxs[i & 7], fmaxf(fmaxf(__uint_as_float(s[0][i]), __uint_as_float(s[1][i])),
+                                             fmaxf(__uint_as_float(s[2][i]), __uint_as_float(s[3][i]))));
+      const float mx = fmaxf(fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])),
+                             fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
       const float m_new = fmaxf(m_used, mx * scale_log2);
       const bool grow = (m_new - m_used) > kRescaleThreshold;   // false for NaN (-inf - -inf)
       if (__any_sync(0xffffffffu, grow)) {
@@ -199,21 +207,27 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
         }
       }
       const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used;
-      float sum = 0.f;
+      float sums[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         uint32_t p[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           const int e = c * 64 + 2 * i;
-          const float p0 = fast_exp2(fmaf(__uint_as_float(s[e >> 5][e & 31]), scale_log2, neg_m));
-          const float p1 = fast_exp2(fmaf(__uint_as_float(s[(e + 1) >> 5][(e + 1) & 31]), scale_log2, neg_m));
-          sum += p0 + p1;
+          const float x0 = fmaf(__uint_as_float(s[e >> 5][e & 31]), scale_log2, neg_m);
+          const float x1 = fmaf(__uint_as_float(s[(e + 1) >> 5][(e + 1) & 31]), scale_log2, neg_m);
+          // EXPMODE: share of the exponentials evaluated on the FMA pipe instead of the SFU
+          //   0 none, 1 one in four, 2 one in two, 3 all, 4 = timing experiment only (no exp at all)
+          const bool poly0 = EXPMODE == 3 || (EXPMODE == 2) || (EXPMODE == 1 && (i & 1) == 0);
+          const bool poly1 = EXPMODE == 3;
+          const float p0 = EXPMODE == 4 ? x0 : (poly0 ? poly_exp2(x0) : fast_exp2(x0));
+          const float p1 = EXPMODE == 4 ? x1 : (poly1 ? poly_exp2(x1) : fast_exp2(x1));
+          sums[i & 3] += p0 + p1;
           p[i] = pack2<T>(p0, p1);
         }
         tc::st32(s_addr + c * 32, p);
       }
-      l += sum;
+      l += (sums[0] + sums[1]) + (sums[2] + sums[3]);
       tc::wait_st();
       tc::fence_before_sync();
       mbar_arrive(p_full + 8 * x);
@@ -242,63 +256,68 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
     }
     tc::fence_before_sync();
   } else if (warp == kExtMmaWarp) {
-    // ============================================================ MMA issuer (one thread)
+    // ============================================================ MMA issuer
+    // The whole warp runs the loop with uniform control flow (descriptors, addresses and counters
+    // stay in uniform registers, which is where UTCHMMA takes its operands from); one elected lane
+    // issues the tcgen05 instructions.
     tc::setmaxnreg_dec<88>();
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc_s = tc::instr_desc<T>(128, kExtKvTile, 0, 0);
       constexpr uint32_t idesc_pv = tc::instr_desc<T>(128, D, 0, 1);
-      // Operand tiles were written by cp.async (generic proxy) and are read by the tensor core
-      // (async proxy): wait for the copies, then order the two proxies before issuing.
+      const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
       auto wait_tile = [&](int u) {
         mbar_wait_guarded(full0 + 8 * (u % RING), (u / RING) & 1);
         fence_proxy_async_smem();
         tc::fence_after_sync();
       };
-      auto issue_s = [&](int x, int u) {
-        const uint32_t qa = q_smem + x * C::TILE_BYTES, kb = ring_smem + (u % RING) * C::TILE_BYTES;
+      auto issue_s = [&](int x, int u, bool release_k) {
+        const uint32_t slot = u % RING;
+        const uint32_t qa = q_smem + x * C::TILE_BYTES, kb = ring_smem + slot * C::TILE_BYTES;
+        if (tc::elect_one()) {
 #pragma unroll
-        for (int kk = 0; kk < D / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * C::HALF_BYTES + (kk & 3) * 32;
-          tc::mma_ss(tmem + x * 128, tc::smem_desc_sw128(qa + off, 16, 1024),
-                     tc::smem_desc_sw128(kb + off, 16, 1024), idesc_s, kk > 0);
+          for (int kk = 0; kk < D / 16; ++kk) {
+            const uint32_t off = (kk >> 2) * C::HALF_BYTES + (kk & 3) * 32;
+            tc::mma_ss(tm + x * 128, tc::smem_desc_sw128(qa + off, 16, 1024),
+                       tc::smem_desc_sw128(kb + off, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
+          }
+          tc::commit(s_full + 8 * x);
+          if (release_k) tc::commit(empty0 + 8 * slot);
         }
+        __syncwarp();
       };
-      auto issue_pv = [&](int x, int u, bool acc) {
-        const uint32_t vb = ring_smem + (u % RING) * C::TILE_BYTES;
+      auto issue_pv = [&](int x, int u, bool acc, bool release_v, bool last) {
+        const uint32_t slot = u % RING;
+        const uint32_t vb = ring_smem + slot * C::TILE_BYTES;
+        if (tc::elect_one()) {
 #pragma unroll
-        for (int kk = 0; kk < kExtKvTile / 16; ++kk) {
-          // 16 KV tokens per step = two 8-row groups (SBO 1024 B); 64-wide D blocks LBO apart
-          tc::mma_ts(tmem + C::O_COL + x * D, tmem + x * 128 + kk * 8,
-                     tc::smem_desc_sw128(vb + kk * 2048, C::HALF_BYTES, 1024), idesc_pv, acc || kk > 0);
+          for (int kk = 0; kk < kExtKvTile / 16; ++kk) {
+            tc::mma_ts(tm + C::O_COL + x * D, tm + x * 128 + kk * 8,
+                       tc::smem_desc_sw128(vb + kk * 2048, C::HALF_BYTES, 1024), idesc_pv, (acc || kk > 0) ? 1u : 0u);
+          }
+          if (release_v) tc::commit(empty0 + 8 * slot);
+          if (last) tc::commit(s_full + 8 * x);     // O_X complete
         }
+        __syncwarp();
       };
       mbar_wait_guarded(q_full, 0);
       wait_tile(0);
-      issue_s(0, 0);
-      tc::commit(s_full);
-      issue_s(1, 0);
-      tc::commit(s_full + 8);
-      tc::commit(empty0);
+      issue_s(0, 0, false);
+      issue_s(1, 0, true);
       for (int j = 0; j < nkv; ++j) {
         const int uv = 2 * j + 1, uk = 2 * j + 2;     // V_j, K_{j+1}
         wait_tile(uv);
+#pragma unroll
         for (int x = 0; x < 2; ++x) {
           mbar_wait_guarded(p_full + 8 * x, j & 1);
           tc::fence_after_sync();
-          issue_pv(x, uv, j > 0);
-          if (x == 1) tc::commit(empty0 + 8 * (uv % RING));
+          issue_pv(x, uv, j > 0, x == 1, j + 1 >= nkv);
           if (j + 1 < nkv) {
             if (x == 0) wait_tile(uk);
-            issue_s(x, uk);
-            tc::commit(s_full + 8 * x);
-            if (x == 1) tc::commit(empty0 + 8 * (uk % RING));
-          } else {
-            tc::commit(s_full + 8 * x);     // O_X complete
+            issue_s(x, uk, x == 1);
           }
         }
       }
     }
-    __syncwarp();
   } else {
     // ============================================================ producers: gather Q, K_j, V_j
     tc::setmaxnreg_dec<88>();
@@ -368,13 +387,13 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
 // ------------------------------------------------------------------------------------ launcher
 namespace bsgl {
 
-template <typename T, int D>
+template <typename T, int D, int EXPMODE>
 static int launch_extend(const void* q, const void* k_slab, const void* v_slab, const int32_t* req_to_token,
                          int64_t pt_stride, const int64_t* req_pool_indices, const int64_t* prefix_lens,
                          const int32_t* qo_indptr, int batch, int64_t n_tokens, int n_q_heads, int n_kv_heads,
                          float sm_scale, void* out, cudaStream_t stream) {
   using C = ExtCfg<D>;
-  auto kern = extend_attention_kernel<T, D>;
+  auto kern = extend_attention_kernel<T, D, EXPMODE>;
   static thread_local int configured_dev = -1;
   int dev = 0;
   BSGL_CUDA_TRY(cudaGetDevice(&dev));
@@ -419,9 +438,21 @@ extern "C" int bsgl_extend_attention(const void* q, const void* k_slab, const vo
                    ((uintptr_t)out % 16 == 0),
                "bsgl_extend_attention: pointers must be 16-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
-#define BSGL_EXT(T, D)                                                                                              \
-  return launch_extend<T, D>(q, k_slab, v_slab, req_to_token, page_table_stride, req_pool_indices, prefix_lens,    \
-                             qo_indptr, batch, n_tokens, n_q_heads, n_kv_heads, sm_scale, out, s)
+  static const int expmode = [] {
+    const char* e = getenv("BSGL_EXT_EXPMODE");
+    return e ? atoi(e) : 0;
+  }();
+#define BSGL_EXT1(T, D, M)                                                                                          \
+  return launch_extend<T, D, M>(q, k_slab, v_slab, req_to_token, page_table_stride, req_pool_indices, prefix_lens, \
+                                qo_indptr, batch, n_tokens, n_q_heads, n_kv_heads, sm_scale, out, s)
+#define BSGL_EXT(T, D)                    \
+  do {                                    \
+    if (expmode == 1) BSGL_EXT1(T, D, 1); \
+    if (expmode == 2) BSGL_EXT1(T, D, 2); \
+    if (expmode == 3) BSGL_EXT1(T, D, 3); \
+    if (expmode == 4) BSGL_EXT1(T, D, 4); \
+    BSGL_EXT1(T, D, 0);                   \
+  } while (0)
   if (dtype == BSGL_BF16) {
     if (head_dim == 128) BSGL_EXT(__nv_bfloat16, 128);
     BSGL_EXT(__nv_bfloat16, 64);
@@ -429,4 +460,5 @@ extern "C" int bsgl_extend_attention(const void* q, const void* k_slab, const vo
   if (head_dim == 128) BSGL_EXT(__half, 128);
   BSGL_EXT(__half, 64);
 #undef BSGL_EXT
+#undef BSGL_EXT1
 }

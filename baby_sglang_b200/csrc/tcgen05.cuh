@@ -10,6 +10,17 @@
 namespace bsgl {
 namespace tc {
 
+// One lane of the (converged) warp: the surrounding control flow stays warp-uniform.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ---------------------------------------------------------------- TMEM allocation (one warp)
 __device__ __forceinline__ void tmem_alloc(uint32_t smem_result_addr, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_result_addr),
@@ -135,6 +146,20 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 template <int N>
 __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// 2^x on the FMA pipe (no SFU): Cody-Waite split x = floor(x) + r, r in [0,1), a degree-3 minimax
+// polynomial for 2^r (relative error ~1e-4, far below the 2^-9 rounding of a 16-bit P), and the integer
+// part added straight into the exponent field.  Valid for x in [-126, 126]; smaller x clamps to 2^-126.
+__device__ __forceinline__ float poly_exp2(float x) {
+  x = fmaxf(x, -126.f);
+  float t;
+  asm("add.rm.ftz.f32 %0, %1, %2;" : "=f"(t) : "f"(x), "f"(12582912.f));   // 1.5 * 2^23 + floor(x)
+  const float r = x - (t - 12582912.f);
+  float p = fmaf(0.077119089663028717f, r, 0.227564394474029541f);
+  p = fmaf(p, r, 0.695146143436431885f);
+  p = fmaf(p, r, 1.0f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
 
 // mbarrier wait that traps instead of hanging the GPU if the pipeline protocol is ever violated.
