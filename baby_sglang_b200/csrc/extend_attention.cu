@@ -51,9 +51,9 @@ struct ExtCfg {
   static constexpr int Q_OFF = 0;
   static constexpr int RING_OFF = 2 * TILE_BYTES;
   static constexpr int BAR_OFF = RING_OFF + RING * TILE_BYTES;
-  static constexpr int N_BARS = 1 + 2 * RING + 4;        // q_full, full/empty per slot, s_full[2], p_full[2]
+  static constexpr int N_BARS = 1 + 2 * RING + 6;        // q_full, full/empty per slot, s_full[2], p_lo[2], p_hi[2]
   static constexpr int MISC_OFF = BAR_OFF + N_BARS * 8;
-  static constexpr int SMEM_BYTES = MISC_OFF + 64 + 1024;   // + alignment slack
+  static constexpr int SMEM_BYTES = MISC_OFF + 64;
   static_assert(SMEM_BYTES <= 227 * 1024, "extend kernel shared memory over budget");
   static constexpr int TMEM_COLS = 512;
   static constexpr int O_COL = 256;
@@ -74,9 +74,10 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
                         const int32_t* __restrict__ qo_indptr, int batch, int n_q_heads, int n_kv_heads,
                         float scale_log2, T* __restrict__ out) {
   using C = ExtCfg<D>;
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  uint8_t* smem = smem_raw + (smem_base - smem_u32(smem_raw));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];   // SWIZZLE_128B operand tiles need 1024-byte alignment
+  const uint32_t smem_base = smem_u32(smem_raw);
+  if (smem_base & 1023u) __trap();
+  uint8_t* smem = smem_raw;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = n_q_heads / n_kv_heads;
   const int TQ = kExtRows / G;                // tokens per chunk
@@ -132,7 +133,8 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
     }
     for (int x = 0; x < 2; ++x) {
       mbar_init(s_full + 8 * x, 1);
-      mbar_init(p_full + 8 * x, 128);
+      mbar_init(p_full + 8 * x, 128);        // P columns 0..31  (KV tokens 0..63 of the tile)
+      mbar_init(p_full + 16 + 8 * x, 128);   // P columns 32..63 (KV tokens 64..127)
     }
     fence_mbar_init();
   }
@@ -220,17 +222,19 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
           //   0 none, 1 one in four, 2 one in two, 3 all, 4 = timing experiment only (no exp at all)
           const bool poly0 = EXPMODE == 3 || (EXPMODE == 2) || (EXPMODE == 1 && (i & 1) == 0);
           const bool poly1 = EXPMODE == 3;
-          const float p0 = EXPMODE == 4 ? x0 : (poly0 ? poly_exp2(x0) : fast_exp2(x0));
-          const float p1 = EXPMODE == 4 ? x1 : (poly1 ? poly_exp2(x1) : fast_exp2(x1));
+          const float p0 = (EXPMODE == 4 || EXPMODE == 6) ? x0 : (poly0 ? poly_exp2(x0) : fast_exp2(x0));
+          const float p1 = (EXPMODE == 4 || EXPMODE == 6) ? x1 : (poly1 ? poly_exp2(x1) : fast_exp2(x1));
           sums[i & 3] += p0 + p1;
           p[i] = pack2<T>(p0, p1);
         }
         tc::st32(s_addr + c * 32, p);
+        // hand each half of P to the MMA warp as soon as it is stored: the first half of PV_X
+        // runs under the second half's exponentials
+        tc::wait_st();
+        tc::fence_before_sync();
+        mbar_arrive(p_full + 16 * c + 8 * x);
       }
       l += (sums[0] + sums[1]) + (sums[2] + sums[3]);
-      tc::wait_st();
-      tc::fence_before_sync();
-      mbar_arrive(p_full + 8 * x);
     }
     // ---- epilogue: O / l -> out[token, head, :]
     mbar_wait_guarded(s_full + 8 * x, nkv & 1);
@@ -285,17 +289,18 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
         }
         __syncwarp();
       };
-      auto issue_pv = [&](int x, int u, bool acc, bool release_v, bool last) {
+      auto issue_pv = [&](int x, int u, int hlf, bool acc, bool release_v, bool last) {
         const uint32_t slot = u % RING;
         const uint32_t vb = ring_smem + slot * C::TILE_BYTES;
         if (tc::elect_one()) {
 #pragma unroll
-          for (int kk = 0; kk < kExtKvTile / 16; ++kk) {
+          for (int k4 = 0; k4 < kExtKvTile / 32; ++k4) {
+            const int kk = hlf * (kExtKvTile / 32) + k4;
             tc::mma_ts(tm + C::O_COL + x * D, tm + x * 128 + kk * 8,
                        tc::smem_desc_sw128(vb + kk * 2048, C::HALF_BYTES, 1024), idesc_pv, (acc || kk > 0) ? 1u : 0u);
           }
-          if (release_v) tc::commit(empty0 + 8 * slot);
-          if (last) tc::commit(s_full + 8 * x);     // O_X complete
+          if (hlf == 1 && release_v) tc::commit(empty0 + 8 * slot);
+          if (hlf == 1 && last) tc::commit(s_full + 8 * x);     // O_X complete
         }
         __syncwarp();
       };
@@ -308,9 +313,12 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
         wait_tile(uv);
 #pragma unroll
         for (int x = 0; x < 2; ++x) {
-          mbar_wait_guarded(p_full + 8 * x, j & 1);
-          tc::fence_after_sync();
-          issue_pv(x, uv, j > 0, x == 1, j + 1 >= nkv);
+#pragma unroll
+          for (int hlf = 0; hlf < 2; ++hlf) {
+            mbar_wait_guarded(p_full + 16 * hlf + 8 * x, j & 1);
+            tc::fence_after_sync();
+            issue_pv(x, uv, hlf, j > 0, x == 1, j + 1 >= nkv);
+          }
           if (j + 1 < nkv) {
             if (x == 0) wait_tile(uk);
             issue_s(x, uk, x == 1);
@@ -363,7 +371,7 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
 #pragma unroll
         for (int i = 0; i < C::NR; ++i) {
           const int r = r0 + i * C::RSTEP;
-          if (r < kExtKvTile) {
+          if (r < kExtKvTile && !((EXPMODE == 5 || EXPMODE == 6) && u >= RING)) {   // 5/6: timing experiment, no gather
             const bool ok = idx[i] >= 0;
             cp_async16_zfill(dst + dst_of(r), base + (ok ? idx[i] : 0) * slab_row, ok ? 16u : 0u);
           }
@@ -451,6 +459,8 @@ extern "C" int bsgl_extend_attention(const void* q, const void* k_slab, const vo
     if (expmode == 2) BSGL_EXT1(T, D, 2); \
     if (expmode == 3) BSGL_EXT1(T, D, 3); \
     if (expmode == 4) BSGL_EXT1(T, D, 4); \
+    if (expmode == 5) BSGL_EXT1(T, D, 5); \
+    if (expmode == 6) BSGL_EXT1(T, D, 6); \
     BSGL_EXT1(T, D, 0);                   \
   } while (0)
   if (dtype == BSGL_BF16) {

@@ -134,6 +134,15 @@ __device__ __forceinline__ void st32(uint32_t taddr, const uint32_t (&r)[32]) {
       : "memory");
 }
 
+__device__ __forceinline__ void st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+        "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+
 }  // namespace tc
 
 // 16-byte cp.async with zero fill: copies src_bytes (0 or 16) and zero-fills the rest.
@@ -166,7 +175,7 @@ __device__ __forceinline__ float poly_exp2(float x) {
 __device__ __forceinline__ void mbar_wait_guarded(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 24)) __trap();   // try_wait suspends ~microseconds per try: tens of seconds
+    if (++spins > (1u << 19)) __trap();   // try_wait suspends ~microseconds per try: about a second
   }
 }
 
