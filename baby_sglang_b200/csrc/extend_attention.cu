@@ -39,6 +39,7 @@ constexpr int kExtThreads = (kExtSoftmaxWarps + 1 + kExtProducerWarps) * 32;   /
 constexpr int kExtRows = 256;        // packed q rows per chunk (2 MMA tiles)
 constexpr int kExtKvTile = 128;      // KV tokens per tile
 constexpr float kRescaleThreshold = 8.f;   // log2 units
+constexpr int kExtPParts = 2;        // P is handed to the MMA warp in this many column groups per tile
 
 template <int D>
 struct ExtCfg {
@@ -51,7 +52,7 @@ struct ExtCfg {
   static constexpr int Q_OFF = 0;
   static constexpr int RING_OFF = 2 * TILE_BYTES;
   static constexpr int BAR_OFF = RING_OFF + RING * TILE_BYTES;
-  static constexpr int N_BARS = 1 + 2 * RING + 6;        // q_full, full/empty per slot, s_full[2], p_lo[2], p_hi[2]
+  static constexpr int N_BARS = 1 + 2 * RING + 2 + 2 * kExtPParts;   // q_full, full/empty per slot, s_full[2], p_full[parts][2]
   static constexpr int MISC_OFF = BAR_OFF + N_BARS * 8;
   static constexpr int SMEM_BYTES = MISC_OFF + 64;
   static_assert(SMEM_BYTES <= 227 * 1024, "extend kernel shared memory over budget");
@@ -71,8 +72,8 @@ __global__ void __launch_bounds__(kExtThreads, 1)
 extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, const T* __restrict__ v_slab,
                         const int32_t* __restrict__ req_to_token, int64_t pt_stride,
                         const int64_t* __restrict__ req_pool_indices, const int64_t* __restrict__ prefix_lens,
-                        const int32_t* __restrict__ qo_indptr, int batch, int n_q_heads, int n_kv_heads,
-                        float scale_log2, T* __restrict__ out) {
+                        const int32_t* __restrict__ qo_indptr, const int32_t* __restrict__ req_order, int batch,
+                        int n_q_heads, int n_kv_heads, float scale_log2, T* __restrict__ out) {
   using C = ExtCfg<D>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];   // SWIZZLE_128B operand tiles need 1024-byte alignment
   const uint32_t smem_base = smem_u32(smem_raw);
@@ -81,16 +82,18 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = n_q_heads / n_kv_heads;
   const int TQ = kExtRows / G;                // tokens per chunk
-  const int h = blockIdx.y;                   // KV head
+  const int h = blockIdx.x % n_kv_heads;      // KV head: fastest, so the heads of one chunk run together
 
-  // ---- which (request, chunk) is this CTA?  chunk counts are ceil(ext_i / TQ); warp 0 scans them.
+  // ---- which (request, chunk) is this CTA?  chunk counts are ceil(ext_i / TQ); warp 0 scans them in
+  // dispatch order (req_order: longest KV first, so the last wave is made of the cheapest requests).
   ExtItem* item = reinterpret_cast<ExtItem*>(smem + C::MISC_OFF + 16);
   if (warp == 0) {
-    const int target = blockIdx.x;
+    const int target = blockIdx.x / n_kv_heads;
     int base = 0, found = 0;
     for (int i0 = 0; i0 < batch && !found; i0 += 32) {
-      const int i = i0 + lane;
-      const int cnt = i < batch ? (qo_indptr[i + 1] - qo_indptr[i] + TQ - 1) / TQ : 0;
+      const int pos = i0 + lane;
+      const int i = pos < batch ? (req_order ? req_order[pos] : pos) : 0;
+      const int cnt = pos < batch ? (qo_indptr[i + 1] - qo_indptr[i] + TQ - 1) / TQ : 0;
       int incl = cnt;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -133,8 +136,7 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
     }
     for (int x = 0; x < 2; ++x) {
       mbar_init(s_full + 8 * x, 1);
-      mbar_init(p_full + 8 * x, 128);        // P columns 0..31  (KV tokens 0..63 of the tile)
-      mbar_init(p_full + 16 + 8 * x, 128);   // P columns 32..63 (KV tokens 64..127)
+      for (int c = 0; c < kExtPParts; ++c) mbar_init(p_full + 16 * c + 8 * x, 128);   // P column group c of tile x
     }
     fence_mbar_init();
   }
@@ -211,15 +213,16 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
       const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used;
       float sums[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t p[32];
+      for (int c = 0; c < kExtPParts; ++c) {
+        constexpr int NP = 64 / kExtPParts;               // packed P columns per group
+        uint32_t p[NP];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int e = c * 64 + 2 * i;
+        for (int i = 0; i < NP; ++i) {
+          const int e = c * 2 * NP + 2 * i;
           const float x0 = fmaf(__uint_as_float(s[e >> 5][e & 31]), scale_log2, neg_m);
           const float x1 = fmaf(__uint_as_float(s[(e + 1) >> 5][(e + 1) & 31]), scale_log2, neg_m);
           // EXPMODE: share of the exponentials evaluated on the FMA pipe instead of the SFU
-          //   0 none, 1 one in four, 2 one in two, 3 all, 4 = timing experiment only (no exp at all)
+          //   0 none, 1 one in four, 2 one in two, 3 all; 4/5/6 = timing experiments only
           const bool poly0 = EXPMODE == 3 || (EXPMODE == 2) || (EXPMODE == 1 && (i & 1) == 0);
           const bool poly1 = EXPMODE == 3;
           const float p0 = (EXPMODE == 4 || EXPMODE == 6) ? x0 : (poly0 ? poly_exp2(x0) : fast_exp2(x0));
@@ -227,9 +230,9 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
           sums[i & 3] += p0 + p1;
           p[i] = pack2<T>(p0, p1);
         }
-        tc::st32(s_addr + c * 32, p);
-        // hand each half of P to the MMA warp as soon as it is stored: the first half of PV_X
-        // runs under the second half's exponentials
+        tc::st_cols(s_addr + c * NP, p);
+        // hand each column group of P to the MMA warp as soon as it is stored: PV_X of the earlier
+        // groups runs under the later groups' exponentials
         tc::wait_st();
         tc::fence_before_sync();
         mbar_arrive(p_full + 16 * c + 8 * x);
@@ -294,13 +297,13 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
         const uint32_t vb = ring_smem + slot * C::TILE_BYTES;
         if (tc::elect_one()) {
 #pragma unroll
-          for (int k4 = 0; k4 < kExtKvTile / 32; ++k4) {
-            const int kk = hlf * (kExtKvTile / 32) + k4;
+          for (int k4 = 0; k4 < kExtKvTile / 16 / kExtPParts; ++k4) {
+            const int kk = hlf * (kExtKvTile / 16 / kExtPParts) + k4;
             tc::mma_ts(tm + C::O_COL + x * D, tm + x * 128 + kk * 8,
                        tc::smem_desc_sw128(vb + kk * 2048, C::HALF_BYTES, 1024), idesc_pv, (acc || kk > 0) ? 1u : 0u);
           }
-          if (hlf == 1 && release_v) tc::commit(empty0 + 8 * slot);
-          if (hlf == 1 && last) tc::commit(s_full + 8 * x);     // O_X complete
+          if (hlf == kExtPParts - 1 && release_v) tc::commit(empty0 + 8 * slot);
+          if (hlf == kExtPParts - 1 && last) tc::commit(s_full + 8 * x);     // O_X complete
         }
         __syncwarp();
       };
@@ -314,7 +317,7 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
 #pragma unroll
         for (int x = 0; x < 2; ++x) {
 #pragma unroll
-          for (int hlf = 0; hlf < 2; ++hlf) {
+          for (int hlf = 0; hlf < kExtPParts; ++hlf) {
             mbar_wait_guarded(p_full + 16 * hlf + 8 * x, j & 1);
             tc::fence_after_sync();
             issue_pv(x, uv, hlf, j > 0, x == 1, j + 1 >= nkv);
@@ -398,8 +401,8 @@ namespace bsgl {
 template <typename T, int D, int EXPMODE>
 static int launch_extend(const void* q, const void* k_slab, const void* v_slab, const int32_t* req_to_token,
                          int64_t pt_stride, const int64_t* req_pool_indices, const int64_t* prefix_lens,
-                         const int32_t* qo_indptr, int batch, int64_t n_tokens, int n_q_heads, int n_kv_heads,
-                         float sm_scale, void* out, cudaStream_t stream) {
+                         const int32_t* qo_indptr, const int32_t* req_order, int batch, int64_t n_tokens,
+                         int n_q_heads, int n_kv_heads, float sm_scale, void* out, cudaStream_t stream) {
   using C = ExtCfg<D>;
   auto kern = extend_attention_kernel<T, D, EXPMODE>;
   static thread_local int configured_dev = -1;
@@ -413,12 +416,12 @@ static int launch_extend(const void* q, const void* k_slab, const void* v_slab, 
   const int TQ = kExtRows / G;
   // sum_i ceil(ext_i / TQ) <= floor(T / TQ) + batch; surplus CTAs exit before touching TMEM
   const int64_t max_chunks = n_tokens / TQ + batch;
-  BSGL_REQUIRE(max_chunks < (1ll << 31), "bsgl_extend_attention: too many q chunks");
-  dim3 grid((unsigned)max_chunks, (unsigned)n_kv_heads);
+  BSGL_REQUIRE(max_chunks * n_kv_heads < (1ll << 31), "bsgl_extend_attention: too many q chunks");
+  dim3 grid((unsigned)(max_chunks * n_kv_heads));
   const float scale_log2 = sm_scale * 1.4426950408889634f;
   kern<<<grid, kExtThreads, C::SMEM_BYTES, stream>>>((const T*)q, (const T*)k_slab, (const T*)v_slab, req_to_token,
-                                                     pt_stride, req_pool_indices, prefix_lens, qo_indptr, batch,
-                                                     n_q_heads, n_kv_heads, scale_log2, (T*)out);
+                                                     pt_stride, req_pool_indices, prefix_lens, qo_indptr, req_order,
+                                                     batch, n_q_heads, n_kv_heads, scale_log2, (T*)out);
   return check_launch("extend_attention_kernel");
 }
 
@@ -427,8 +430,8 @@ static int launch_extend(const void* q, const void* k_slab, const void* v_slab, 
 extern "C" int bsgl_extend_attention(const void* q, const void* k_slab, const void* v_slab,
                                      const int32_t* req_to_token, int64_t page_table_stride,
                                      const int64_t* req_pool_indices, const int64_t* seq_lens,
-                                     const int64_t* prefix_lens, const int32_t* qo_indptr, int batch,
-                                     int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim, float sm_scale,
+                                     const int64_t* prefix_lens, const int32_t* qo_indptr,
+                                     const int32_t* req_order, int batch, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim, float sm_scale,
                                      int dtype, void* out, void* stream) {
   using namespace bsgl;
   (void)seq_lens;   // seq = prefix + ext; ext comes from qo_indptr
@@ -452,7 +455,7 @@ extern "C" int bsgl_extend_attention(const void* q, const void* k_slab, const vo
   }();
 #define BSGL_EXT1(T, D, M)                                                                                          \
   return launch_extend<T, D, M>(q, k_slab, v_slab, req_to_token, page_table_stride, req_pool_indices, prefix_lens, \
-                                qo_indptr, batch, n_tokens, n_q_heads, n_kv_heads, sm_scale, out, s)
+                                qo_indptr, req_order, batch, n_tokens, n_q_heads, n_kv_heads, sm_scale, out, s)
 #define BSGL_EXT(T, D)                    \
   do {                                    \
     if (expmode == 1) BSGL_EXT1(T, D, 1); \

@@ -10,6 +10,7 @@
 namespace bsgl {
 
 constexpr int kMetaThreads = 1024;
+constexpr int kMaxSortedBatch = 4096;   // larger batches keep request order (B^2 / 1024 comparisons per thread)
 
 // Exclusive block scan of a packed (hi = a, lo = b) pair of non-negative 32-bit counts.
 __device__ __forceinline__ unsigned long long block_excl_scan(unsigned long long v, unsigned long long* warp_tot,
@@ -112,8 +113,25 @@ __global__ void __launch_bounds__(kMetaThreads) extend_metadata_kernel(
     const int64_t* __restrict__ prefix_lens, int B, int64_t T, int nhg, int n_ctas,
     int64_t* __restrict__ extended_lens, int64_t* __restrict__ positions, int32_t* __restrict__ qo_indptr,
     int32_t* __restrict__ kv_indptr, int64_t* __restrict__ row_idx_off, int32_t* __restrict__ row_kv_len,
-    int32_t* __restrict__ plan_hdr, int32_t* __restrict__ tile_indptr, int32_t* __restrict__ cta_first_seq) {
+    int32_t* __restrict__ plan_hdr, int32_t* __restrict__ tile_indptr, int32_t* __restrict__ cta_first_seq,
+    int32_t* __restrict__ heavy_order) {
   __shared__ unsigned long long warp_tot[33];
+  // phase 0: requests by descending seq_len (rank by counting; ties keep index order)
+  if (heavy_order != nullptr) {
+    __shared__ int32_t keys[kMaxSortedBatch];
+    if (B <= kMaxSortedBatch) {
+      for (int i = threadIdx.x; i < B; i += kMetaThreads) keys[i] = (int32_t)seq_lens[i];
+      __syncthreads();
+      for (int i = threadIdx.x; i < B; i += kMetaThreads) {
+        const int32_t k = keys[i];
+        int rank = 0;
+        for (int j = 0; j < B; ++j) rank += (keys[j] > k) || (keys[j] == k && j < i);
+        heavy_order[rank] = i;
+      }
+    } else {
+      for (int i = threadIdx.x; i < B; i += kMetaThreads) heavy_order[i] = i;
+    }
+  }
   // phase 1: per request
   unsigned carry_q = 0, carry_kv = 0;
   for (int base = 0; base < B; base += kMetaThreads) {
@@ -211,7 +229,7 @@ int bsgl_build_extend_metadata(int64_t page_table_stride, const int64_t* req_poo
                                const int64_t* prefix_lens, int batch, int64_t n_tokens, int n_head_groups, int n_ctas,
                                int64_t* extended_lens, int64_t* positions, int32_t* qo_indptr, int32_t* kv_indptr,
                                int64_t* row_idx_off, int32_t* row_kv_len, int32_t* plan_hdr, int32_t* tile_indptr,
-                               int32_t* cta_first_seq, void* stream) {
+                               int32_t* cta_first_seq, int32_t* heavy_order, void* stream) {
   using namespace bsgl;
   BSGL_REQUIRE(batch >= 0 && n_tokens >= 0 && n_head_groups > 0 && n_ctas > 0,
                "bsgl_build_extend_metadata: bad sizes");
@@ -223,7 +241,8 @@ int bsgl_build_extend_metadata(int64_t page_table_stride, const int64_t* req_poo
   BSGL_REQUIRE(n_tokens * n_head_groups < (1ll << 31), "bsgl_build_extend_metadata: too many rows");
   extend_metadata_kernel<<<1, kMetaThreads, 0, (cudaStream_t)stream>>>(
       page_table_stride, req_pool_indices, seq_lens, prefix_lens, batch, n_tokens, n_head_groups, n_ctas,
-      extended_lens, positions, qo_indptr, kv_indptr, row_idx_off, row_kv_len, plan_hdr, tile_indptr, cta_first_seq);
+      extended_lens, positions, qo_indptr, kv_indptr, row_idx_off, row_kv_len, plan_hdr, tile_indptr, cta_first_seq,
+      heavy_order);
   return check_launch("extend_metadata_kernel");
 }
 

@@ -143,6 +143,9 @@ __device__ __forceinline__ void st16(uint32_t taddr, const uint32_t (&r)[16]) {
       : "memory");
 }
 
+__device__ __forceinline__ void st_cols(uint32_t taddr, const uint32_t (&r)[32]) { st32(taddr, r); }
+__device__ __forceinline__ void st_cols(uint32_t taddr, const uint32_t (&r)[16]) { st16(taddr, r); }
+
 }  // namespace tc
 
 // 16-byte cp.async with zero fill: copies src_bytes (0 or 16) and zero-fills the rest.

@@ -130,6 +130,7 @@ class BatchMetadata:
     extended_lens: Optional[torch.Tensor]      # int64 [B] (extend only)
     plan: Optional[AttnPlan]
     kv_indices: Optional[torch.Tensor] = None  # int32 [sum(seq)] (built on request)
+    heavy_order: Optional[torch.Tensor] = None  # int32 [B] requests by descending seq_len (extend only)
 
 
 def _plan_buffers(dev, n_rows: int, nhg: int, n_ctas: int):
@@ -189,18 +190,19 @@ def build_extend_metadata(req_to_token: torch.Tensor, req_pool_indices: torch.Te
     kv_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
     qo_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
     row_idx_off, row_kv_len, plan_hdr, tile_indptr, cta_first_seq = _plan_buffers(dev, T, nhg, n_ctas)
+    heavy_order = torch.empty(B, dtype=torch.int32, device=dev)
     null = ctypes.c_void_p(0)
     rc = _lib.load().bsgl_build_extend_metadata(
         req_to_token.stride(0), rpi.data_ptr(), sl.data_ptr(), pl.data_ptr(), B, T, nhg, n_ctas,
         extended.data_ptr(), positions.data_ptr(), qo_indptr.data_ptr(), kv_indptr.data_ptr(),
         row_idx_off.data_ptr(), row_kv_len.data_ptr(),
         plan_hdr.data_ptr() if row_plan else null, tile_indptr.data_ptr() if row_plan else null,
-        cta_first_seq.data_ptr() if row_plan else null, _stream())
+        cta_first_seq.data_ptr() if row_plan else null, heavy_order.data_ptr(), _stream())
     _lib.check(rc, "bsgl_build_extend_metadata")
     _count()
     plan = AttnPlan(T, int(n_kv_heads), nhg, n_ctas, row_idx_off, row_kv_len, plan_hdr, tile_indptr,
                     cta_first_seq) if row_plan else None
-    return BatchMetadata(positions, kv_indptr, qo_indptr, extended, plan)
+    return BatchMetadata(positions, kv_indptr, qo_indptr, extended, plan, heavy_order=heavy_order)
 
 
 def gather_kv_indices(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
@@ -288,10 +290,12 @@ def extend_mode(n_tokens: int, batch: int) -> str:
 
 def extend_attention_tc(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor, req_to_token: torch.Tensor,
                         req_pool_indices: torch.Tensor, seq_lens: torch.Tensor, prefix_lens: torch.Tensor,
-                        qo_indptr: torch.Tensor, sm_scale: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                        qo_indptr: torch.Tensor, sm_scale: float, out: Optional[torch.Tensor] = None,
+                        req_order: Optional[torch.Tensor] = None) -> torch.Tensor:
     """K3: ragged extend attention on tcgen05/TMEM (reference `_prefill_attention`,
     attn_backend.py:34-110).  q rows are packed in request order (`qo_indptr`); request i's row r
-    sees KV columns 0..prefix_i + r of its page-table row."""
+    sees KV columns 0..prefix_i + r of its page-table row.  `req_order` (K4's `heavy_order`) only
+    changes the order in which requests are dispatched to the SMs, never the result."""
     dev = _require_cuda(q, k_slab, v_slab, req_to_token, req_pool_indices, seq_lens, prefix_lens, qo_indptr)
     if q.dim() != 3:
         raise _lib.BsglError(f"q must be [tokens, Hq, D], got {tuple(q.shape)}")
@@ -311,9 +315,13 @@ def extend_attention_tc(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Ten
     if T == 0 or B == 0:
         return out
     rpi, sl, pl = _as_i64(req_pool_indices), _as_i64(seq_lens), _as_i64(prefix_lens)
+    if req_order is not None and (req_order.dtype != torch.int32 or int(req_order.shape[0]) != B or
+                                  not req_order.is_cuda):
+        raise _lib.BsglError("req_order must be a CUDA int32 tensor of length batch")
     rc = _lib.load().bsgl_extend_attention(
         q.data_ptr(), k_slab.data_ptr(), v_slab.data_ptr(), req_to_token.data_ptr(), req_to_token.stride(0),
-        rpi.data_ptr(), sl.data_ptr(), pl.data_ptr(), qo_indptr.data_ptr(), B, T, Hq, Hkv, D, float(sm_scale),
+        rpi.data_ptr(), sl.data_ptr(), pl.data_ptr(), qo_indptr.data_ptr(),
+        req_order.data_ptr() if req_order is not None else ctypes.c_void_p(0), B, T, Hq, Hkv, D, float(sm_scale),
         dtype_code(q.dtype), out.data_ptr(), _stream())
     _lib.check(rc, "bsgl_extend_attention")
     _count()
@@ -333,7 +341,7 @@ def extend_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor
     mode = mode or extend_mode(int(q.shape[0]), B)
     if mode == "tcgen05":
         return extend_attention_tc(q, k_slab, v_slab, r2t, forward_batch.req_pool_indices, forward_batch.seq_lens,
-                                   forward_batch.prefix_lens, md.qo_indptr, sm_scale)
+                                   forward_batch.prefix_lens, md.qo_indptr, sm_scale, req_order=md.heavy_order)
     if md.plan is None:   # metadata was built for the tensor-core path: add the row plan now
         full = build_extend_metadata(r2t, forward_batch.req_pool_indices, forward_batch.seq_lens,
                                      forward_batch.prefix_lens, int(q.shape[0]), int(k_slab.shape[1]),

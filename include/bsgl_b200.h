@@ -98,7 +98,9 @@ int bsgl_build_decode_metadata(int64_t page_table_stride, const int64_t* req_poo
  *   row_idx_off   int64 [T], row_kv_len int32 [T]  per q token: its request's page-table row
  *                              and prefix + local_row + 1 (mask col <= prefix+row, attn_backend.py:83-85)
  *   plan_hdr / tile_indptr [T*n_head_groups+1] / cta_first_seq [n_ctas+1]: row-wise plan
- *                              (may be NULL when the row-wise kernel will not be used). */
+ *                              (may be NULL when the row-wise kernel will not be used).
+ *   heavy_order   int32 [B]    request indices by descending seq_len (ties by index): the dispatch
+ *                              order of bsgl_extend_attention's CTAs (may be NULL). */
 int bsgl_build_extend_metadata(int64_t page_table_stride, const int64_t* req_pool_indices,
                                const int64_t* seq_lens, const int64_t* prefix_lens, int batch,
                                int64_t n_tokens, int n_head_groups, int n_ctas,
@@ -106,7 +108,7 @@ int bsgl_build_extend_metadata(int64_t page_table_stride, const int64_t* req_poo
                                int32_t* qo_indptr, int32_t* kv_indptr,
                                int64_t* row_idx_off, int32_t* row_kv_len,
                                int32_t* plan_hdr, int32_t* tile_indptr, int32_t* cta_first_seq,
-                               void* stream);
+                               int32_t* heavy_order, void* stream);
 
 /* kv_indices[kv_indptr[i] + p] = req_to_token[req_pool_indices[i], p] for p < seq_lens[i]. */
 int bsgl_gather_kv_indices(const int32_t* req_to_token, int64_t page_table_stride,
@@ -140,12 +142,14 @@ int bsgl_merge_partials(const float* part_o, const float* part_lse, const int32_
 
 /* K3.  Ragged extend attention (radix-cache prefix + new tokens) on tcgen05/TMEM tensor cores.
  * q rows are packed in request order (qo_indptr); request i's row r sees KV columns
- * 0..prefix_lens[i]+r of req_to_token[req_pool_indices[i], :seq_lens[i]]. */
+ * 0..prefix_lens[i]+r of req_to_token[req_pool_indices[i], :seq_lens[i]].  req_order (int32 [B], a
+ * permutation of 0..B-1, NULL = identity) is the order in which requests are handed to the SMs;
+ * K4's heavy_order (longest KV first) shortens the tail of ragged batches.  It never changes results. */
 int bsgl_extend_attention(const void* q, const void* k_slab, const void* v_slab,
                           const int32_t* req_to_token, int64_t page_table_stride,
                           const int64_t* req_pool_indices, const int64_t* seq_lens,
                           const int64_t* prefix_lens, const int32_t* qo_indptr,
-                          int batch, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim,
+                          const int32_t* req_order, int batch, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim,
                           float sm_scale, int dtype, void* out, void* stream);
 
 #ifdef __cplusplus

@@ -59,6 +59,7 @@ def main():
     ap.add_argument("--ext", type=int, default=512)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--mode", default="tcgen05", choices=["tcgen05", "rowwise"])
+    ap.add_argument("--no-order", action="store_true", help="dispatch requests in index order (no heavy-first)")
     a = ap.parse_args()
     w = build(a.geom, a.batch, a.max_prefix, a.ext, fixed_prefix=a.fixed_prefix)
     dev = w["q"].device
@@ -70,7 +71,7 @@ def main():
     def run():
         if a.mode == "tcgen05":
             ops.extend_attention_tc(w["q"], w["k_slab"], w["v_slab"], w["r2t"], w["rpi"], seq, pre, md.qo_indptr,
-                                    scale, out=out)
+                                    scale, out=out, req_order=None if a.no_order else md.heavy_order)
         else:
             ops.paged_attention(w["q"], w["k_slab"], w["v_slab"], w["r2t"], md.plan, scale, out=out)
 

@@ -49,7 +49,13 @@ def _run_backend(ops, c, dtype=torch.bfloat16, n_ctas=None, store=True, extend_m
             out = ops.paged_attention(q, k_slab, v_slab, r2t, md.plan, c.D ** -0.5)
         else:
             out = ops.extend_attention_tc(q, k_slab, v_slab, r2t, c.req_pool_indices.cuda(), c.seq_lens.cuda(),
-                                          c.prefix_lens.cuda(), md.qo_indptr, c.D ** -0.5)
+                                          c.prefix_lens.cuda(), md.qo_indptr, c.D ** -0.5, req_order=md.heavy_order)
+            # the dispatch order is bit-exact (stable, longest KV first) and never changes the result
+            want = torch.sort(c.seq_lens, descending=True, stable=True).indices.to(torch.int32)
+            assert torch.equal(md.heavy_order.cpu(), want)
+            plain = ops.extend_attention_tc(q, k_slab, v_slab, r2t, c.req_pool_indices.cuda(), c.seq_lens.cuda(),
+                                            c.prefix_lens.cuda(), md.qo_indptr, c.D ** -0.5)
+            assert torch.equal(out, plain)
     else:
         md = ops.build_decode_metadata(r2t, c.req_pool_indices.cuda(), c.seq_lens.cuda(), c.Hkv, n_ctas=n_ctas)
         out = ops.paged_attention(q, k_slab, v_slab, r2t, md.plan, c.D ** -0.5)
