@@ -303,6 +303,9 @@ def run_b200(args, rank, world, device):
             out = after_attention(attn_backend.SimpleAttentionBackend.forward(q, k, v, w["layers"][l], fb, True))
         return out
 
+    from baby_sglang_b200.host_staging import HostStagedAttention
+    staged = HostStagedAttention(Hq, Hkv, D, device)
+
     def step_e2e():
         rpi = rpi_host.to(device, non_blocking=True)
         seq = seq_host.to(device, non_blocking=True)
@@ -311,11 +314,8 @@ def run_b200(args, rank, world, device):
         fb = forward_batch.SimplifiedForwardBatch.create_decode_batch(
             input_ids=ids, req_pool_indices=rpi, seq_lens=seq, out_cache_loc=loc,
             req_to_token_pool=w["r2t_pool"], token_to_kv_pool=w["kv_pool"])
-        for l in range(L):
-            q, k, v = split(qkv_host[l].to(device, non_blocking=True))
-            out = after_attention(attn_backend.SimpleAttentionBackend.forward(q, k, v, w["layers"][l], fb, True))
-            out_host[l].copy_(out, non_blocking=True)
-        torch.cuda.current_stream().synchronize()   # the caller reads out_host
+        # uploads of layer l+1 and downloads of layer l overlap layer l's kernels (host_staging.py)
+        staged.forward_layers(qkv_host, out_host, w["layers"], fb, after=after_attention if with_oproj else None)
         return out_host[L - 1]
 
     def barrier():
@@ -421,7 +421,7 @@ def run_b200(args, rank, world, device):
         "decode_tok_per_s_attention_path": round(world * B / (ms_step / 1e3), 1),
         "e2e": {"value": round(e2e_v, 1), "unit": "GB/s", "ms_per_step": round(ms_e2e, 4),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "api": "dropin attn_backend.SimpleAttentionBackend.forward from pinned host q/k/v"},
+                "api": "HostStagedAttention.forward_layers (dropin attn_backend.SimpleAttentionBackend.forward per layer) from pinned host q/k/v, copies on side streams"},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "paged_attention_kernel", "achieved": round(achieved, 1),

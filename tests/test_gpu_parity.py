@@ -265,3 +265,60 @@ def test_cpu_tensors_are_refused(ops):
         ops.kv_store(torch.zeros(3, 1, 64, dtype=torch.bfloat16), torch.zeros(3, 1, 64, dtype=torch.bfloat16),
                      torch.tensor([1], dtype=torch.int32), torch.zeros(1, 1, 64, dtype=torch.bfloat16),
                      torch.zeros(1, 1, 64, dtype=torch.bfloat16))
+
+
+def test_host_staged_layers_match_direct_calls(ops):
+    """HostStagedAttention (pinned host q/k/v in, host outputs out, copies on side streams) returns
+    bit-for-bit what per-layer calls of the drop-in backend return, for decode and extend."""
+    from baby_sglang_b200 import DROPIN_DIR
+    from baby_sglang_b200.host_staging import HostStagedAttention
+    if DROPIN_DIR not in sys.path:
+        sys.path.insert(0, DROPIN_DIR)
+    import attn_backend
+    import forward_batch
+    import memory_pool
+
+    Hq, Hkv, D, L = 12, 2, 128, 3
+    for prefill in (False, True):
+        seq = [300, 17, 129, 64]
+        pre = [260, 0, 100, 1] if prefill else None
+        c = make_paged_case(B=4, Hq=Hq, Hkv=Hkv, D=D, seq_lens=seq, prefix_lens=pre, seed=5)
+        T = c.qkv.shape[0]
+
+        class Layer:
+            def __init__(self, i):
+                self.layer_id, self.head_dim, self.scaling = i, D, D ** -0.5
+                self.tp_q_head_num, self.tp_k_head_num, self.tp_v_head_num = Hq, Hkv, Hkv
+
+        layers = [Layer(i) for i in range(L)]
+        g = torch.Generator().manual_seed(3)
+        qkv_host = [torch.randn(T, (Hq + 2 * Hkv) * D, generator=g).to(torch.bfloat16).pin_memory() for _ in range(L)]
+
+        def fresh():
+            kv = memory_pool.MHATokenToKVPool(size=c.S, dtype=torch.bfloat16, head_num=Hkv, head_dim=D, layer_num=L,
+                                              device="cuda")
+            for l in range(L):
+                kv.k_buffer[l].copy_(c.k_slab)
+                kv.v_buffer[l].copy_(c.v_slab)
+            r2t = memory_pool.ReqToTokenPool(size=c.req_to_token.shape[0], max_context_len=c.C, device="cuda")
+            r2t.req_to_token.copy_(c.req_to_token)
+            common = dict(input_ids=torch.zeros(T, dtype=torch.int64, device="cuda"),
+                          req_pool_indices=c.req_pool_indices.cuda(), seq_lens=c.seq_lens.cuda(),
+                          out_cache_loc=c.out_cache_loc.cuda(), req_to_token_pool=r2t, token_to_kv_pool=kv)
+            if prefill:
+                return forward_batch.SimplifiedForwardBatch.create_prefill_batch(prefix_lens=c.prefix_lens.cuda(), **common)
+            return forward_batch.SimplifiedForwardBatch.create_decode_batch(**common)
+
+        fb = fresh()
+        direct = []
+        for l in range(L):
+            x = qkv_host[l].cuda()
+            q, k, v = x.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+            direct.append(attn_backend.SimpleAttentionBackend.forward(
+                q.contiguous().view(T, Hq, D), k.contiguous().view(T, Hkv, D), v.view(T, Hkv, D), layers[l], fb, True).cpu())
+        fb2 = fresh()
+        out_host = [torch.empty(T, Hq * D, dtype=torch.bfloat16).pin_memory() for _ in range(L)]
+        HostStagedAttention(Hq, Hkv, D, torch.device("cuda")).forward_layers(qkv_host, out_host, layers, fb2)
+        for l in range(L):
+            assert torch.equal(out_host[l], direct[l]), f"layer {l} prefill={prefill}"
+            assert torch.equal(fb.token_to_kv_pool.k_buffer[l], fb2.token_to_kv_pool.k_buffer[l])
