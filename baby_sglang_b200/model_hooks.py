@@ -1,0 +1,87 @@
+"""Model-side hooks for the steps immediately before and after the attention path.
+
+The reference model (qwen2.py) stays unchanged on disk; these functions mutate a loaded model
+*instance*, the same mechanism `tp_runtime.shard_attention_heads` uses for KV-head TP.
+
+`install_fused_rope_kv_store(model)`
+    Replaces, per `Qwen2Attention.forward` (qwen2.py:179-197): the q/k/v split of the fused
+    projection (:185, QKVLinear.forward :285-290), `rotary_emb` (:191, RotaryEmbedding.forward
+    :249-268: cos/sin, four products, two `torch.cat`) and `set_kv_buffer` (memory_pool.py:152-171)
+    by ONE launch of K5 (`bsgl_rope_kv_store`): rotated q comes back contiguous, rotated K and V go
+    straight into the paged slabs.  Attention then runs with `save_kv_cache=False` on the drop-in
+    backend, reading the rows K5 just stored (store-before-attend order, attn_backend.py:20-32).
+
+There is no fallback: on CPU tensors the kernels raise.
+"""
+from __future__ import annotations
+
+import types
+from typing import List
+
+import torch
+
+from . import ops
+
+
+def _attention_modules(model: torch.nn.Module):
+    """Modules shaped like the reference's Qwen2Attention (qwen2.py:143-177)."""
+    for m in model.modules():
+        inner = getattr(getattr(m, "qkv_proj", None), "qkv_proj", None)
+        if isinstance(inner, torch.nn.Linear) and isinstance(getattr(m, "o_proj", None), torch.nn.Linear) \
+                and hasattr(m, "attn") and hasattr(m, "rotary_emb") and hasattr(m, "num_kv_heads"):
+            yield m
+
+
+def _inv_freq_f32(rotary: torch.nn.Module) -> torch.Tensor:
+    """`inv_freq` as the fp32 values the reference multiplies with.  The loader casts the whole model, buffers
+    included, to the 16-bit dtype (model_loader.py:77), and `torch.outer(positions.float(), inv_freq)`
+    (qwen2.py:251) promotes it back: the VALUES are the rounded ones.  Cached per buffer."""
+    inv = rotary.inv_freq
+    if inv.dtype == torch.float32:
+        return inv
+    key = (inv.data_ptr(), inv.dtype, inv.device, inv._version)
+    cached = rotary.__dict__.get("_bsgl_inv_freq_f32")
+    if cached is None or cached[0] != key:
+        cached = (key, inv.to(torch.float32))
+        rotary.__dict__["_bsgl_inv_freq_f32"] = cached
+    return cached[1]
+
+
+def _fused_attention_forward(self, positions: torch.Tensor, hidden_states: torch.Tensor, forward_batch):
+    """Drop-in for Qwen2Attention.forward (qwen2.py:179-197) with K5 in place of split + RoPE + store."""
+    import attn_backend   # the drop-in module (first on sys.path wherever the reference stack runs)
+
+    qkv = self.qkv_proj.qkv_proj(hidden_states)                      # the fused Linear (qwen2.py:283)
+    pool = forward_batch.token_to_kv_pool
+    layer_id = self.attn.layer_id
+    k_slab, v_slab = pool.get_kv_buffer(layer_id)
+    if qkv.dtype != k_slab.dtype:
+        # the reference casts k/v to the pool dtype inside set_kv_buffer (memory_pool.py:163-165);
+        # the fused store keeps one dtype end to end
+        raise RuntimeError(f"fused RoPE store needs activation dtype {qkv.dtype} == KV pool dtype {k_slab.dtype}")
+    q = ops.rope_kv_store(qkv, positions, _inv_freq_f32(self.rotary_emb), self.num_heads, self.num_kv_heads,
+                          self.head_dim, k_slab, v_slab, forward_batch.out_cache_loc)
+    attn_output = attn_backend.SimpleAttentionBackend.forward(q, None, None, self.attn, forward_batch, False)
+    return self.o_proj(attn_output)
+
+
+def install_fused_rope_kv_store(model: torch.nn.Module) -> int:
+    """Route every attention module of `model` through K5.  Returns the number of modules patched.
+    Works on a model already sharded by `tp_runtime.shard_attention_heads` (it reads the patched
+    `num_heads` / `num_kv_heads`, and the all-reduce hook on `o_proj` still fires)."""
+    mods: List[torch.nn.Module] = list(_attention_modules(model))
+    if not mods:
+        raise ValueError("model has no attention modules of the expected shape")
+    for m in mods:
+        if m.head_dim % 16 != 0:
+            raise ValueError(f"head_dim {m.head_dim} is not a multiple of 16")
+        if not torch.is_tensor(getattr(m.rotary_emb, "inv_freq", None)):
+            raise ValueError("rotary_emb has no inv_freq buffer (qwen2.py:244-245)")
+        m.forward = types.MethodType(_fused_attention_forward, m)
+    return len(mods)
+
+
+def uninstall_fused_rope_kv_store(model: torch.nn.Module) -> None:
+    """Restore the class-level forward of every patched attention module."""
+    for m in _attention_modules(model):
+        m.__dict__.pop("forward", None)

@@ -107,6 +107,55 @@ def kv_store(k_slab: torch.Tensor, v_slab: torch.Tensor, loc: torch.Tensor,
     _count()
 
 
+# --------------------------------------------------------------------------------------- K5
+def rope_kv_store(qkv: torch.Tensor, positions: torch.Tensor, inv_freq: torch.Tensor, n_q_heads: int,
+                  n_kv_heads: int, head_dim: int, k_slab: Optional[torch.Tensor] = None,
+                  v_slab: Optional[torch.Tensor] = None, loc: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """RoPE + q/k/v split + KV store in one launch (reference qwen2.py:249-268, 285-290 and
+    memory_pool.py:152-171).  `qkv` is the fused projection output `[T, (Hq + 2 Hkv) D]`; returns the
+    rotated q `[T, Hq, D]`.  With slabs and `loc` the rotated K rows and the V rows are written to
+    `slab[loc[t]]`; without them only q is rotated."""
+    _require_cuda(qkv, positions, inv_freq, k_slab, v_slab, loc)
+    Hq, Hkv, D = int(n_q_heads), int(n_kv_heads), int(head_dim)
+    if qkv.dim() != 2 or qkv.shape[1] != (Hq + 2 * Hkv) * D or qkv.stride(1) != 1:
+        raise _lib.BsglError(f"qkv must be [T, (Hq + 2 Hkv) * D] with unit inner stride, got {tuple(qkv.shape)}")
+    T = int(qkv.shape[0])
+    store = k_slab is not None
+    if store:
+        if v_slab is None or loc is None:
+            raise _lib.BsglError("k_slab, v_slab and loc go together")
+        if k_slab.dtype != qkv.dtype or v_slab.dtype != qkv.dtype:
+            raise _lib.BsglError("the fused RoPE store needs activation dtype == KV pool dtype")
+        if tuple(k_slab.shape[1:]) != (Hkv, D) or not (k_slab.is_contiguous() and v_slab.is_contiguous()):
+            raise _lib.BsglError("KV slabs must be contiguous [S+1, Hkv, D]")
+        if loc.dtype != torch.int32:
+            loc = loc.to(torch.int32)
+        loc = loc.contiguous()
+        if int(loc.shape[0]) != T:
+            raise _lib.BsglError("loc must have one slot per token")
+    if positions.dtype != torch.int64:
+        positions = positions.to(torch.int64)
+    positions = positions.contiguous()
+    if int(positions.shape[0]) != T:
+        raise _lib.BsglError("positions must have one entry per token")
+    if inv_freq.dtype != torch.float32 or int(inv_freq.numel()) != D // 2:
+        raise _lib.BsglError("inv_freq must be float32 [D/2]")
+    inv_freq = inv_freq.contiguous()
+    if qkv.stride(0) % 8 != 0 or qkv.data_ptr() % 16 != 0:
+        qkv = qkv.contiguous()
+    q_out = torch.empty((T, Hq, D), dtype=qkv.dtype, device=qkv.device)
+    if T == 0:
+        return q_out
+    null = ctypes.c_void_p(0)
+    rc = _lib.load().bsgl_rope_kv_store(
+        qkv.data_ptr(), qkv.stride(0), positions.data_ptr(), inv_freq.data_ptr(),
+        loc.data_ptr() if store else null, k_slab.data_ptr() if store else null,
+        v_slab.data_ptr() if store else null, q_out.data_ptr(), T, Hq, Hkv, D, dtype_code(qkv.dtype), _stream())
+    _lib.check(rc, "bsgl_rope_kv_store")
+    _count()
+    return q_out
+
+
 # --------------------------------------------------------------------------------------- K4
 @dataclass
 class AttnPlan:

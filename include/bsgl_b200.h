@@ -21,6 +21,7 @@
  *                               row-wise extend for short extends          attn_backend.py:34-110
  *   bsgl_merge_partials         (no counterpart: LSE merge of the split-KV partials)
  *   bsgl_extend_attention       _prefill_attention                         attn_backend.py:34-110
+ *   bsgl_rope_kv_store          RotaryEmbedding.forward + split + set_kv_buffer qwen2.py:249-290
  *
  * Layout conventions (identical to the reference's tensors):
  *   q        [rows, n_q_heads, head_dim]            contiguous, bf16 or fp16
@@ -151,6 +152,20 @@ int bsgl_extend_attention(const void* q, const void* k_slab, const void* v_slab,
                           const int64_t* prefix_lens, const int32_t* qo_indptr,
                           const int32_t* req_order, int batch, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim,
                           float sm_scale, int dtype, void* out, void* stream);
+
+/* K5 (the step immediately before the path).  RoPE + q/k/v split of the fused
+ * projection output + KV store in one launch.  Replaces RotaryEmbedding.forward/_apply_rope
+ * (qwen2.py:249-268), the split (qwen2.py:285-290) and set_kv_buffer (memory_pool.py:152-171).
+ *   qkv       [T, (Hq + 2*Hkv) * D] rows qkv_row_stride elements apart (the Linear's output)
+ *   positions int64 [T], inv_freq float32 [D/2] (the module's own buffer, qwen2.py:244-245)
+ *   q_out     [T, Hq, D] contiguous, rotated
+ *   k_slab/v_slab[loc[t]] receive the rotated K row and the V row; all three NULL = rotate q only.
+ * Rounding follows the reference: cos/sin rounded to the activation dtype, every product and sum
+ * rounded to it (bit-exact against the reference run on the same device). */
+int bsgl_rope_kv_store(const void* qkv, int64_t qkv_row_stride, const int64_t* positions,
+                       const float* inv_freq, const int32_t* loc, void* k_slab, void* v_slab,
+                       void* q_out, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim,
+                       int dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -258,3 +258,49 @@ def merge_partials(o_parts: torch.Tensor, lse2_parts: torch.Tensor) -> Tuple[tor
     den = w.sum(dim=0)
     o = (w[:, :, None] * o_parts).sum(dim=0) / den[:, None]
     return o, m + torch.log2(den)
+
+
+# --------------------------------------------------------------------------------------
+# K5  RoPE + split + store   (qwen2.py:249-268, 285-290; memory_pool.py:152-171)
+# --------------------------------------------------------------------------------------
+
+
+def _round_to(x: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    """One elementwise torch op on a 16-bit tensor: compute in fp32, round to nearest even."""
+    return x.to(dtype).to(torch.float32)
+
+
+def rope(positions: torch.Tensor, x: torch.Tensor, inv_freq: torch.Tensor) -> torch.Tensor:
+    """RotaryEmbedding.forward + _apply_rope for one tensor x [T, H, D] (qwen2.py:249-268).
+
+    freqs = outer(positions.float(), inv_freq) in fp32 (:251); cos/sin in fp32 (:252-253) and then
+    cast to x's dtype (:262-263); the rotation `cat([x1*cos - x2*sin, x1*sin + x2*cos])` (:266-268)
+    is evaluated in x's dtype, i.e. every product and every sum is rounded to it.  Restated with
+    explicit fp32 arithmetic and explicit roundings; returns x's dtype."""
+    dt = x.dtype
+    T, H, D = x.shape
+    half = D // 2
+    freqs = positions.to(torch.float32)[:, None] * inv_freq.to(torch.float32)[None, :]
+    cos = _round_to(torch.cos(freqs), dt)[:, None, :]
+    sin = _round_to(torch.sin(freqs), dt)[:, None, :]
+    xf = x.to(torch.float32)
+    x1, x2 = xf[..., :half], xf[..., half:]
+    o1 = _round_to(_round_to(x1 * cos, dt) - _round_to(x2 * sin, dt), dt)
+    o2 = _round_to(_round_to(x1 * sin, dt) + _round_to(x2 * cos, dt), dt)
+    out = torch.empty_like(xf)
+    out[..., :half] = o1
+    out[..., half:] = o2
+    return out.to(dt)
+
+
+def rope_kv_store(qkv: torch.Tensor, positions: torch.Tensor, inv_freq: torch.Tensor, Hq: int, Hkv: int,
+                  D: int, k_slab: torch.Tensor, v_slab: torch.Tensor, loc: torch.Tensor) -> torch.Tensor:
+    """What the model does between the fused projection and attention: split (qwen2.py:285-290),
+    rotate q and k (:185-191), store rotated k and v at `loc` (memory_pool.py:152-171).
+    Returns the rotated q [T, Hq, D]; the slabs are updated in place."""
+    T = qkv.shape[0]
+    q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+    q_rot = rope(positions, q.reshape(T, Hq, D), inv_freq)
+    k_rot = rope(positions, k.reshape(T, Hkv, D), inv_freq)
+    kv_store(k_slab, v_slab, loc, k_rot, v.reshape(T, Hkv, D))
+    return q_rot

@@ -76,7 +76,33 @@ class _AttnLayer(nn.Module):
         self.head_dim, self.scaling, self.layer_id = head_dim, head_dim ** -0.5, layer_id
 
 
+class _Rotary(nn.Module):
+    """Same surface as the reference's RotaryEmbedding (qwen2.py:227-268): an `inv_freq` buffer built on the CPU
+    at construction (and therefore cast along with the model, model_loader.py:77) and forward(positions, q, k)."""
+
+    def __init__(self, head_dim: int, theta: float):
+        super().__init__()
+        inv = 1.0 / (theta ** (torch.arange(0, head_dim, 2).float() / head_dim))
+        self.register_buffer("inv_freq", inv, persistent=False)
+
+    def forward(self, positions, q, k):
+        return _rope(q, positions, self.inv_freq), _rope(k, positions, self.inv_freq)
+
+
 class _SelfAttn(nn.Module):
+    """Same attributes and forward(positions, hidden_states, forward_batch) as the reference's Qwen2Attention
+    (qwen2.py:143-197); `backend` is the drop-in boundary (SimpleAttentionBackend.forward)."""
+    backend: Callable = None
+
+    def forward(self, positions, hidden_states, forward_batch):
+        qkv = self.qkv_proj.qkv_proj(hidden_states)
+        q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
+        q = q.view(-1, self.num_heads, self.head_dim)
+        k = k.view(-1, self.num_kv_heads, self.head_dim)
+        v = v.view(-1, self.num_kv_heads, self.head_dim)        # strided view of the fused output
+        q, k = self.rotary_emb(positions, q, k)
+        return self.o_proj(self.backend(q, k, v, self.attn, forward_batch, True))
+
     def __init__(self, cfg: HarnessConfig, layer_id: int):
         super().__init__()
         self.hidden_size = cfg.hidden_size
@@ -87,6 +113,7 @@ class _SelfAttn(nn.Module):
         self.o_proj = nn.Linear(self.q_size, cfg.hidden_size, bias=False)
         self.attn = _AttnLayer(self.num_heads, self.head_dim, self.num_kv_heads, layer_id)
         self.rope_theta = cfg.rope_theta
+        self.rotary_emb = _Rotary(self.head_dim, cfg.rope_theta)
 
 
 class _Mlp(nn.Module):
@@ -113,12 +140,11 @@ class _Body(nn.Module):
         self.norm = _Norm(cfg.hidden_size, cfg.rms_norm_eps)
 
 
-def _rope(x: torch.Tensor, positions: torch.Tensor, theta: float) -> torch.Tensor:
+def _rope(x: torch.Tensor, positions: torch.Tensor, inv_freq: torch.Tensor) -> torch.Tensor:
     """neox-style rotation of [T, H, D]: halves (x1, x2) -> (x1 cos - x2 sin, x1 sin + x2 cos); cos/sin are
     computed in fp32 and cast to x's dtype before the multiply (qwen2.py:249-268)."""
     D = x.shape[-1]
-    inv = 1.0 / (theta ** (torch.arange(0, D, 2, device=x.device).float() / D))
-    ang = positions.float()[:, None] * inv[None, :]
+    ang = torch.outer(positions.float(), inv_freq)
     c, s = torch.cos(ang)[:, None, :].to(x.dtype), torch.sin(ang)[:, None, :].to(x.dtype)
     a, b = x[..., : D // 2], x[..., D // 2:]
     return torch.cat((a * c - b * s, a * s + b * c), dim=-1)
@@ -134,6 +160,8 @@ class HarnessQwen2(nn.Module):
         self.model = _Body(cfg)
         self.lm_head = None if cfg.tie_word_embeddings else nn.Linear(cfg.hidden_size, cfg.vocab_size, bias=False)
         self.backend = backend
+        for layer in self.model.layers:
+            layer.self_attn.__dict__["backend"] = backend      # plain attribute, not a submodule
 
     @torch.no_grad()
     def forward(self, input_ids, positions, forward_batch):
@@ -146,14 +174,7 @@ class HarnessQwen2(nn.Module):
             else:
                 res = h + res
             x = _rms(res, layer.input_layernorm.weight, eps)
-            at = layer.self_attn
-            qkv = at.qkv_proj.qkv_proj(x)
-            q, k, v = qkv.split([at.q_size, at.kv_size, at.kv_size], dim=-1)
-            q = _rope(q.view(-1, at.num_heads, at.head_dim), positions, at.rope_theta)
-            k = _rope(k.view(-1, at.num_kv_heads, at.head_dim), positions, at.rope_theta)
-            v = v.view(-1, at.num_kv_heads, at.head_dim)        # strided view of the fused output
-            a = self.backend(q, k, v, at.attn, forward_batch, True)
-            h = at.o_proj(a)
+            h = layer.self_attn(positions, x, forward_batch)
             res = h + res
             x = _rms(res, layer.post_attention_layernorm.weight, eps)
             gate, up = layer.mlp.gate_up_proj.gate_up_proj(x).chunk(2, dim=-1)

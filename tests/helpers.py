@@ -12,7 +12,27 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
 def golden_names(prefix=""):
-    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, prefix + "*.npz")))
+    """Attention fixtures (decode_*/extend_*); the RoPE fixtures are listed by rope_golden_names()."""
+    names = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, prefix + "*.npz")))
+    return [n for n in names if not n.startswith("rope_")]
+
+
+def rope_golden_names():
+    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "rope_*.npz")))
+
+
+def load_rope_golden(name: str) -> SimpleNamespace:
+    """Outputs of the reference's RotaryEmbedding (tests/golden/make_rope_golden.py)."""
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    dt = torch.bfloat16 if int(z["is_bf16"]) else torch.float16
+    bits = lambda a: torch.from_numpy(a.astype(np.int16)).view(dt)   # noqa: E731
+    g = SimpleNamespace(name=name, dtype=dt, Hq=int(z["Hq"]), Hkv=int(z["Hkv"]), D=int(z["D"]))
+    g.positions = torch.from_numpy(z["positions"])
+    g.inv_freq = torch.from_numpy(z["inv_freq"])
+    g.qkv = bits(z["qkv"])
+    g.q_rot = bits(z["q_rot"])
+    g.k_rot = bits(z["k_rot"])
+    return g
 
 
 def from_bf16_bits(a: np.ndarray) -> torch.Tensor:

@@ -56,7 +56,12 @@ GPU_CASES = {
 }
 
 
-BF16_ULP = 2.0 ** -8      # relative spacing of bf16 logits (the reference computes logits in the model dtype)
+import math
+
+
+def bf16_ulp(x: float) -> float:
+    """Spacing of bf16 numbers at |x| (8 significant bits): the reference computes logits in the model dtype."""
+    return 2.0 ** (math.floor(math.log2(max(abs(x), 2.0 ** -126))) - 7)
 
 
 def _check_against(ref, got, what):
@@ -69,7 +74,7 @@ def _check_against(ref, got, what):
     for i, (a, b) in enumerate(zip(ref.ids, got.pred)):
         for s_, (x, y) in enumerate(zip(a, b)):
             if x != y:
-                tol = 2 * BF16_ULP * max(abs(ref.top1[i][s_]), 1.0)
+                tol = 2 * bf16_ulp(max(abs(ref.top1[i][s_]), 1.0))
                 (excused if ref.margin[i][s_] <= tol else bad).append((i, s_, ref.margin[i][s_], tol))
     assert not bad, f"{what}: token IDs differ away from ties (request, step, margin, tie tolerance): {bad[:5]}"
     assert len(excused) <= max(2, steps // 20), f"{what}: too many tie flips {len(excused)}/{steps}: {excused[:5]}"
@@ -117,3 +122,35 @@ def test_gpu_greedy_ids_match_oracle_backend(name):
     g = torch.Generator().manual_seed(len(name))
     prompts = [torch.randint(0, kw["vocab_size"], (n,), generator=g).tolist() for n in lens]
     _gpu_compare(kw, prompts, 64, torch.bfloat16)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(GPU_CASES))
+def test_gpu_fused_rope_kv_store_hook_is_bit_identical(name):
+    """`install_fused_rope_kv_store` (K5: split + RoPE + KV store in one launch, attention
+    with save_kv_cache=False) must not change a single bit: same greedy IDs, same logit margins, same KV slabs
+    and page table as the unfused drop-in path (which stores through K1 after torch RoPE)."""
+    from baby_sglang_b200.model_hooks import install_fused_rope_kv_store, uninstall_fused_rope_kv_store
+    from tests.oracle_stack import dropin_stack
+    kw, lens = GPU_CASES[name]
+    g = torch.Generator().manual_seed(len(name))
+    prompts = [torch.randint(0, kw["vocab_size"], (n,), generator=g).tolist() for n in lens]
+    dev, dtype = torch.device("cuda"), torch.bfloat16
+    sd = dropin_stack()
+    m = _model({"config": kw}, sd.backend_forward, dev, dtype)
+    plain = greedy_generate(m, sd, prompts, 24, dev, dtype)
+    assert install_fused_rope_kv_store(m) == kw["num_hidden_layers"]
+    fused = greedy_generate(m, sd, prompts, 24, dev, dtype)
+    assert fused.ids == plain.ids
+    assert fused.top1 == plain.top1 and fused.margin == plain.margin
+    assert torch.equal(plain.pools[0].req_to_token, fused.pools[0].req_to_token)
+    for l in range(kw["num_hidden_layers"]):
+        used = plain.pools[0].req_to_token.flatten().long().unique()
+        assert torch.equal(plain.pools[1].k_buffer[l][used], fused.pools[1].k_buffer[l][used])
+        assert torch.equal(plain.pools[1].v_buffer[l][used], fused.pools[1].v_buffer[l][used])
+    # prefix reuse (extend with prefix > 0) through the fused path
+    reuse = [max(0, (2 * len(p)) // 3) for p in prompts]
+    fused2 = greedy_generate(m, sd, prompts, 24, dev, dtype, reuse_prefix=reuse, pools=fused.pools)
+    uninstall_fused_rope_kv_store(m)
+    plain2 = greedy_generate(m, sd, prompts, 24, dev, dtype, reuse_prefix=reuse, pools=plain.pools)
+    assert fused2.ids == plain2.ids and fused2.margin == plain2.margin

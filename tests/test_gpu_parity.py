@@ -322,3 +322,63 @@ def test_host_staged_layers_match_direct_calls(ops):
         for l in range(L):
             assert torch.equal(out_host[l], direct[l]), f"layer {l} prefill={prefill}"
             assert torch.equal(fb.token_to_kv_pool.k_buffer[l], fb2.token_to_kv_pool.k_buffer[l])
+
+
+# ---------------------------------------------------------------------------- K5 RoPE + split + store
+def _ulp_mismatch(a: torch.Tensor, b: torch.Tensor):
+    """(#elements that differ, max difference in units of the 16-bit pattern)."""
+    ia, ib = a.view(torch.int16).int(), b.view(torch.int16).int()
+    d = (ia - ib).abs()
+    return int((d != 0).sum()), int(d.max()) if d.numel() else 0
+
+
+@pytest.mark.parametrize("name", __import__("tests.helpers", fromlist=["x"]).rope_golden_names())
+def test_rope_kv_store_vs_reference_fixture(ops, name):
+    """K5 against RotaryEmbedding outputs the reference produced (CPU libm cos/sin) and, bit for bit,
+    against the oracle evaluated on the device (CUDA cosf/sinf, what the reference calls on a GPU)."""
+    from tests.helpers import load_rope_golden
+    g = load_rope_golden(name)
+    T = g.qkv.shape[0]
+    S = T + 9
+    gen = torch.Generator().manual_seed(2)
+    loc = (torch.randperm(S, generator=gen)[:T] + 1).to(torch.int32)
+    k_slab = torch.randn(S + 1, g.Hkv, g.D, generator=gen).to(g.dtype).cuda()
+    v_slab = torch.randn(S + 1, g.Hkv, g.D, generator=gen).to(g.dtype).cuda()
+    k0, v0 = k_slab.clone(), v_slab.clone()
+    qkv, pos, inv = g.qkv.cuda(), g.positions.cuda(), g.inv_freq.cuda()
+    q_rot = ops.rope_kv_store(qkv, pos, inv, g.Hq, g.Hkv, g.D, k_slab, v_slab, loc.cuda())
+    torch.cuda.synchronize()
+    # (1) device-evaluated oracle: bit-exact, including every untouched slab row
+    ko, vo = k0.clone(), v0.clone()
+    q_ref = O.rope_kv_store(qkv, pos, inv, g.Hq, g.Hkv, g.D, ko, vo, loc.cuda())
+    assert torch.equal(q_rot.view(torch.int16), q_ref.view(torch.int16))
+    assert torch.equal(k_slab.view(torch.int16), ko.view(torch.int16))
+    assert torch.equal(v_slab.view(torch.int16), vo.view(torch.int16))
+    # (2) the reference's own CPU output: identical up to the last bit of cos/sin on a few elements
+    nq, dq = _ulp_mismatch(q_rot.cpu(), g.q_rot)
+    nk, dk = _ulp_mismatch(k_slab.cpu()[loc.long()], g.k_rot)
+    assert dq <= 1 and dk <= 1, (dq, dk)
+    assert nq <= 0.01 * g.q_rot.numel() and nk <= 0.01 * g.k_rot.numel(), (nq, nk)
+    # (3) rotate-only form leaves the slabs alone
+    k1 = k_slab.clone()
+    q_only = ops.rope_kv_store(qkv, pos, inv, g.Hq, g.Hkv, g.D)
+    assert torch.equal(q_only, q_rot) and torch.equal(k1, k_slab)
+
+
+def test_rope_kv_store_large_and_strided(ops):
+    """Full-size decode/prefill shapes (7B geometry), a row-strided qkv view, positions up to 32K."""
+    Hq, Hkv, D = 28, 4, 128
+    for T in (256, 4099):
+        gen = torch.Generator(device="cuda").manual_seed(T)
+        wide = torch.randn(T, (Hq + 2 * Hkv) * D + 64, device="cuda", generator=gen).to(torch.bfloat16)
+        qkv = wide[:, : (Hq + 2 * Hkv) * D]                     # row stride != row length
+        pos = torch.randint(0, 32768, (T,), device="cuda", generator=gen)
+        inv = (1.0 / (1e6 ** (torch.arange(0, D, 2).float() / D))).cuda()
+        S = T + 3
+        loc = (torch.randperm(S, device="cuda", generator=gen)[:T] + 1).to(torch.int32)
+        k_slab = torch.zeros(S + 1, Hkv, D, device="cuda", dtype=torch.bfloat16)
+        v_slab = torch.zeros_like(k_slab)
+        q_rot = ops.rope_kv_store(qkv, pos, inv, Hq, Hkv, D, k_slab, v_slab, loc)
+        ko, vo = torch.zeros_like(k_slab), torch.zeros_like(v_slab)
+        q_ref = O.rope_kv_store(qkv, pos, inv, Hq, Hkv, D, ko, vo, loc)
+        assert torch.equal(q_rot, q_ref) and torch.equal(k_slab, ko) and torch.equal(v_slab, vo)

@@ -4,7 +4,7 @@ import pytest
 import torch
 
 from oracle import paged_attention_oracle as O
-from tests.helpers import golden_names, load_golden, slab_checksum
+from tests.helpers import golden_names, load_golden, load_rope_golden, rope_golden_names, slab_checksum
 
 # fp32 oracle vs fp32 reference: both are softmax(QK^T/sqrt(D))V in fp32; only summation order differs
 FP32_TOL = 2e-5
@@ -86,3 +86,25 @@ def test_merge_partials_equals_unsplit():
     o, lse2 = O.merge_partials(torch.stack(parts_o), torch.stack(parts_l))
     assert (o - full).abs().max() < 1e-5
     assert (lse2 - torch.logsumexp(s, -1) / torch.log(torch.tensor(2.0))).abs().max() < 1e-5
+
+
+@pytest.mark.parametrize("name", rope_golden_names())
+def test_rope_matches_reference_bit_for_bit(name):
+    """oracle.rope / rope_kv_store vs the reference's RotaryEmbedding run in the same 16-bit dtype."""
+    g = load_rope_golden(name)
+    T = g.qkv.shape[0]
+    q, k, v = g.qkv.split([g.Hq * g.D, g.Hkv * g.D, g.Hkv * g.D], dim=-1)
+    q_rot = O.rope(g.positions, q.reshape(T, g.Hq, g.D), g.inv_freq)
+    k_rot = O.rope(g.positions, k.reshape(T, g.Hkv, g.D), g.inv_freq)
+    assert torch.equal(q_rot.view(torch.int16), g.q_rot.view(torch.int16))
+    assert torch.equal(k_rot.view(torch.int16), g.k_rot.view(torch.int16))
+    # fused form: rotated k and plain v land in the slabs at loc, q comes back rotated
+    S = T + 5
+    k_slab = torch.zeros(S + 1, g.Hkv, g.D, dtype=g.dtype)
+    v_slab = torch.zeros(S + 1, g.Hkv, g.D, dtype=g.dtype)
+    loc = (torch.randperm(S, generator=torch.Generator().manual_seed(1))[:T] + 1).to(torch.int32)
+    q2 = O.rope_kv_store(g.qkv, g.positions, g.inv_freq, g.Hq, g.Hkv, g.D, k_slab, v_slab, loc)
+    assert torch.equal(q2.view(torch.int16), g.q_rot.view(torch.int16))
+    assert torch.equal(k_slab[loc.long()].view(torch.int16), g.k_rot.view(torch.int16))
+    assert torch.equal(v_slab[loc.long()], v.reshape(T, g.Hkv, g.D))
+    assert k_slab[0].abs().sum() == 0
