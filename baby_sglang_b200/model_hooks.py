@@ -85,3 +85,43 @@ def uninstall_fused_rope_kv_store(model: torch.nn.Module) -> None:
     """Restore the class-level forward of every patched attention module."""
     for m in _attention_modules(model):
         m.__dict__.pop("forward", None)
+
+
+# ------------------------------------------------------------------------------------------------------
+# after the path: batched greedy sampling (SURVEY.md 8f rank 2)
+# ------------------------------------------------------------------------------------------------------
+def _batched_sample_next_ids(self, logits: torch.Tensor, batch_requests, mode: str) -> torch.Tensor:
+    """Drop-in for Scheduler._sample_next_ids (scheduler.py:509-546).  Batches where every request is
+    greedy and unconstrained go through K6 in one launch with no `.item()`; any other batch is handed
+    to the reference's own method untouched (sampling / constrained decoding are outside this path)."""
+    if any(req.do_sample or req.constraint_state for req in batch_requests):
+        return type(self)._sample_next_ids(self, logits, batch_requests, mode)
+    B = len(batch_requests)
+    dev = logits.device
+    qo = None
+    if mode == "prefill":      # host lists the scheduler already holds (scheduler.py:514-516): no device sync
+        ends, acc = [0], 0
+        for req in batch_requests:
+            acc += len(req.input_ids) - len(req.prefix_indices)
+            ends.append(acc)
+        qo = torch.tensor(ends, dtype=torch.int32).to(dev, non_blocking=True)
+    prev = indptr = pens = None
+    if any((req.repetition_penalty or 0) > 1.0 and len(req.output_ids) > 0 for req in batch_requests):
+        flat, ptr = [], [0]
+        for req in batch_requests:
+            flat.extend(int(t) for t in req.output_ids)
+            ptr.append(len(flat))
+        prev = torch.tensor(flat, dtype=torch.int64).to(dev, non_blocking=True)
+        indptr = torch.tensor(ptr, dtype=torch.int32).to(dev, non_blocking=True)
+        pens = torch.tensor([float(req.repetition_penalty or 1.0) for req in batch_requests],
+                            dtype=torch.float32).to(dev, non_blocking=True)
+    if logits.dim() != 2:
+        logits = logits.reshape(-1, logits.shape[-1])
+    return ops.greedy_sample(logits, qo, prev, indptr, pens, batch=B)
+
+
+def install_batched_greedy_sampler(scheduler) -> None:
+    """Route `scheduler._sample_next_ids` (an instance of the reference's unchanged Scheduler) through K6."""
+    if not hasattr(type(scheduler), "_sample_next_ids"):
+        raise ValueError("object has no _sample_next_ids method (scheduler.py:509)")
+    scheduler._sample_next_ids = types.MethodType(_batched_sample_next_ids, scheduler)

@@ -397,3 +397,44 @@ def extend_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor
                                      row_plan=True)
         md.plan = full.plan
     return paged_attention(q, k_slab, v_slab, r2t, md.plan, sm_scale)
+
+
+# --------------------------------------------------------------------------------------- K6
+def greedy_sample(logits: torch.Tensor, qo_indptr: Optional[torch.Tensor] = None,
+                  prev_ids: Optional[torch.Tensor] = None, prev_indptr: Optional[torch.Tensor] = None,
+                  penalties: Optional[torch.Tensor] = None, batch: Optional[int] = None) -> torch.Tensor:
+    """Batched greedy next-token ids, int64 [B], on the device (reference scheduler.py:509-546 for
+    `do_sample=False` requests: last-token gather, sample.py:19-36 repetition penalty, argmax).
+    `qo_indptr` (K4) selects each request's last row of a prefill's `[T, V]` logits; without it row i
+    belongs to request i.  `prev_ids`/`prev_indptr`/`penalties` describe the per-request histories."""
+    dev = _require_cuda(logits, qo_indptr, prev_ids, prev_indptr, penalties)
+    if logits.dim() != 2 or logits.stride(1) != 1:
+        raise _lib.BsglError(f"logits must be [rows, vocab] with unit inner stride, got {tuple(logits.shape)}")
+    V = int(logits.shape[1])
+    if qo_indptr is not None:
+        if qo_indptr.dtype != torch.int32:
+            raise _lib.BsglError("qo_indptr must be int32")
+        B = int(qo_indptr.shape[0]) - 1
+    else:
+        B = int(logits.shape[0]) if batch is None else int(batch)
+    have_prev = prev_ids is not None
+    if have_prev:
+        if prev_indptr is None or penalties is None:
+            raise _lib.BsglError("prev_ids, prev_indptr and penalties go together")
+        if prev_ids.dtype != torch.int64 or prev_indptr.dtype != torch.int32 or penalties.dtype != torch.float32:
+            raise _lib.BsglError("prev_ids int64, prev_indptr int32, penalties float32")
+        if int(prev_indptr.shape[0]) != B + 1 or int(penalties.shape[0]) != B:
+            raise _lib.BsglError("prev_indptr / penalties do not match the batch")
+        prev_ids, prev_indptr, penalties = prev_ids.contiguous(), prev_indptr.contiguous(), penalties.contiguous()
+    out = torch.empty(B, dtype=torch.int64, device=dev)
+    if B == 0:
+        return out
+    null = ctypes.c_void_p(0)
+    rc = _lib.load().bsgl_greedy_sample(
+        logits.data_ptr(), logits.stride(0), V, dtype_code(logits.dtype),
+        qo_indptr.data_ptr() if qo_indptr is not None else null, B,
+        prev_ids.data_ptr() if have_prev else null, prev_indptr.data_ptr() if have_prev else null,
+        penalties.data_ptr() if have_prev else null, out.data_ptr(), _stream())
+    _lib.check(rc, "bsgl_greedy_sample")
+    _count()
+    return out

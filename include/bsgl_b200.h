@@ -22,6 +22,7 @@
  *   bsgl_merge_partials         (no counterpart: LSE merge of the split-KV partials)
  *   bsgl_extend_attention       _prefill_attention                         attn_backend.py:34-110
  *   bsgl_rope_kv_store          RotaryEmbedding.forward + split + set_kv_buffer qwen2.py:249-290
+ *   bsgl_greedy_sample          Scheduler._sample_next_ids (greedy requests)   scheduler.py:509-546, sample.py:19-60
  *
  * Layout conventions (identical to the reference's tensors):
  *   q        [rows, n_q_heads, head_dim]            contiguous, bf16 or fp16
@@ -166,6 +167,19 @@ int bsgl_rope_kv_store(const void* qkv, int64_t qkv_row_stride, const int64_t* p
                        const float* inv_freq, const int32_t* loc, void* k_slab, void* v_slab,
                        void* q_out, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim,
                        int dtype, void* stream);
+
+/* K6 (the step immediately after the path).  Batched greedy sampling on the
+ * device: last-token gather (scheduler.py:513-521), repetition penalty over the distinct previous
+ * ids (sample.py:19-36) and argmax (sample.py:59-60) for every request in one launch, no `.item()`.
+ *   logits     [rows, vocab] bf16/fp16/fp32, rows row_stride elements apart
+ *   qo_indptr  int32 [B+1] (K4): request i samples from row qo_indptr[i+1]-1; NULL = row i (decode)
+ *   prev_ids   int64 [prev_indptr[B]] with prev_indptr int32 [B+1], penalties float32 [B]
+ *              (all three NULL = no repetition penalty)
+ *   next_ids   int64 [B]: first index of the row maximum (NaN counts as maximal), like torch.argmax */
+int bsgl_greedy_sample(const void* logits, int64_t row_stride, int vocab, int dtype,
+                       const int32_t* qo_indptr, int batch, const int64_t* prev_ids,
+                       const int32_t* prev_indptr, const float* penalties, int64_t* next_ids,
+                       void* stream);
 
 #ifdef __cplusplus
 }

@@ -304,3 +304,47 @@ def rope_kv_store(qkv: torch.Tensor, positions: torch.Tensor, inv_freq: torch.Te
     k_rot = rope(positions, k.reshape(T, Hkv, D), inv_freq)
     kv_store(k_slab, v_slab, loc, k_rot, v.reshape(T, Hkv, D))
     return q_rot
+
+
+# --------------------------------------------------------------------------------------
+# K6  batched greedy sampling   (scheduler.py:509-546, sample.py:19-60)
+# --------------------------------------------------------------------------------------
+
+
+def greedy_sample(logits: torch.Tensor, extended_lens, prev_ids_per_request, penalties) -> torch.Tensor:
+    """Next token ids for requests decoded with do_sample=False.
+
+    * `extended_lens` (list of ints) not None = prefill: request i samples from row
+      cumsum(extended_lens)[i] - 1 of the packed logits (scheduler.py:513-521); None = row i.
+    * repetition penalty (sample.py:19-36): skipped when penalty <= 1 or the history is empty; otherwise
+      for every DISTINCT previous id `logit = logit / penalty if logit > 0 else logit * penalty`, computed
+      in the logits' dtype.
+    * argmax (sample.py:59-60): first index of the maximum.
+    Explicit per-request, per-id loops over a private copy of each row."""
+    B = len(prev_ids_per_request)
+    if extended_lens is not None:
+        rows, acc = [], 0
+        for n in extended_lens:
+            acc += int(n)
+            rows.append(acc - 1)
+    else:
+        rows = list(range(B))
+    out = []
+    for i in range(B):
+        row = logits[rows[i]].clone()
+        pen = float(penalties[i])
+        prev = [int(t) for t in prev_ids_per_request[i]]
+        if pen > 1.0 and len(prev) > 0:
+            for tid in sorted(set(prev)):
+                val = row[tid]
+                row[tid] = val / pen if float(val) > 0 else val * pen
+        best, best_i = None, 0
+        vals = row.to(torch.float32).tolist()
+        for j, v in enumerate(vals):
+            if v != v:                     # NaN counts as the maximum (torch.argmax)
+                best_i = j
+                break
+            if best is None or v > best:
+                best, best_i = v, j
+        out.append(best_i)
+    return torch.tensor(out, dtype=torch.int64)

@@ -134,3 +134,29 @@ def make_paged_case(*, B, Hq, Hkv, D, seq_lens, prefix_lens=None, seed=0, dtype=
         c.k = k.contiguous().view(T, Hkv, D)
         c.v = v.view(T, Hkv, D)
     return c
+
+
+def load_sample_golden():
+    """Outputs of the reference's Scheduler._sample_next_ids (tests/golden/make_sample_golden.py)."""
+    import json
+    with open(os.path.join(GOLDEN_DIR, "sample_greedy.json")) as f:
+        raw = json.load(f)
+    cases = {}
+    for name, c in raw.items():
+        dt = getattr(torch, c["dtype"])
+        bits = np.asarray(c["logits_bits"], dtype=np.int64)
+        if dt == torch.float32:
+            logits = torch.from_numpy(bits.astype(np.int32)).view(torch.float32)
+        else:
+            logits = torch.from_numpy(bits.astype(np.int16)).view(dt)
+        cases[name] = SimpleNamespace(name=name, dtype=dt, V=c["V"], mode=c["mode"], logits=logits,
+                                      extended_lens=c["extended_lens"], prev_ids=c["prev_ids"],
+                                      penalties=c["penalties"], next_ids=torch.tensor(c["next_ids"], dtype=torch.int64))
+    return cases
+
+
+def prev_ids_csr(prev_ids, device="cpu"):
+    """Per-request histories -> (prev_ids int64, prev_indptr int32)."""
+    flat = [t for p in prev_ids for t in p]
+    indptr = np.concatenate([[0], np.cumsum([len(p) for p in prev_ids])]).astype(np.int32)
+    return (torch.tensor(flat, dtype=torch.int64, device=device), torch.from_numpy(indptr).to(device))

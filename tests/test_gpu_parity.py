@@ -382,3 +382,78 @@ def test_rope_kv_store_large_and_strided(ops):
         ko, vo = torch.zeros_like(k_slab), torch.zeros_like(v_slab)
         q_ref = O.rope_kv_store(qkv, pos, inv, Hq, Hkv, D, ko, vo, loc)
         assert torch.equal(q_rot, q_ref) and torch.equal(k_slab, ko) and torch.equal(v_slab, vo)
+
+
+# ---------------------------------------------------------------------------- K6 batched greedy sampling
+def test_greedy_sample_vs_reference_fixture(ops):
+    from tests.helpers import load_sample_golden, prev_ids_csr
+    for name, c in load_sample_golden().items():
+        prev, indptr = prev_ids_csr(c.prev_ids, "cuda")
+        pens = torch.tensor(c.penalties, dtype=torch.float32, device="cuda")
+        qo = None
+        if c.mode == "prefill":
+            qo = torch.tensor([0] + list(torch.tensor(c.extended_lens).cumsum(0)), dtype=torch.int32, device="cuda")
+        got = ops.greedy_sample(c.logits.cuda(), qo, prev, indptr, pens)
+        assert got.dtype == torch.int64 and torch.equal(got.cpu(), c.next_ids), name
+        if all(p <= 1.0 or not h for p, h in zip(c.penalties, c.prev_ids)):
+            assert torch.equal(ops.greedy_sample(c.logits.cuda(), qo).cpu(), c.next_ids)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_greedy_sample_full_vocab_vs_oracle(ops, dtype):
+    """Qwen2.5 vocabulary (152 064), B=64: ties, NaN rows, histories with repeats, prefill gather, odd row stride."""
+    from tests.helpers import prev_ids_csr
+    V, B = 152064, 64
+    g = torch.Generator().manual_seed(9)
+    ext = torch.randint(1, 4, (B,), generator=g).tolist()
+    T = sum(ext)
+    wide = (torch.randn(T, V + 8, generator=g) * 4).to(dtype)
+    logits = wide[:, :V]
+    ends = torch.tensor(ext).cumsum(0) - 1
+    for i in range(B):
+        r = int(ends[i])
+        j = int(torch.argmax(logits[r].float()))
+        if i % 3 == 0:
+            logits[r, (j * 7 + 1) % V] = logits[r, j]                # exact tie: lowest index wins
+        if i == 5:
+            logits[r, 4242] = float("nan")
+    prev = [[] if i % 4 == 0 else torch.topk(logits[int(ends[i])].float(), 3).indices.tolist() * 2 +
+            torch.randint(0, V, (50,), generator=g).tolist() for i in range(B)]
+    pens = [1.0 + (i % 5) * 0.35 for i in range(B)]
+    want = O.greedy_sample(logits, ext, prev, pens)
+    p, ip = prev_ids_csr(prev, "cuda")
+    qo = torch.tensor([0] + torch.tensor(ext).cumsum(0).tolist(), dtype=torch.int32, device="cuda")
+    got = ops.greedy_sample(wide.cuda()[:, :V], qo, p, ip, torch.tensor(pens, dtype=torch.float32, device="cuda"))
+    assert torch.equal(got.cpu(), want)
+    # decode form (row i = request i), no penalty: plain argmax with first-index ties
+    dec = logits[ends]
+    got2 = ops.greedy_sample(dec.cuda().contiguous())
+    assert torch.equal(got2.cpu(), O.greedy_sample(dec, None, [[]] * B, [1.0] * B))
+
+
+def test_batched_greedy_sampler_hook(ops):
+    """`install_batched_greedy_sampler` on an object with the reference scheduler's method: greedy batches go
+    through K6 (ids equal to the fixture the reference produced), other batches reach the original method."""
+    from types import SimpleNamespace
+    from baby_sglang_b200.model_hooks import install_batched_greedy_sampler
+    from tests.helpers import load_sample_golden
+
+    class FakeScheduler:
+        calls = 0
+
+        def _sample_next_ids(self, logits, batch_requests, mode):     # stands in for scheduler.py:509-546
+            FakeScheduler.calls += 1
+            return torch.full((len(batch_requests),), -7, dtype=torch.long, device=logits.device)
+
+    sched = FakeScheduler()
+    install_batched_greedy_sampler(sched)
+    for name, c in load_sample_golden().items():
+        reqs = []
+        for i, e in enumerate(c.extended_lens):
+            reqs.append(SimpleNamespace(input_ids=list(range(e + 2)), prefix_indices=[0, 1], constraint_state=None,
+                                        do_sample=False, output_ids=c.prev_ids[i], repetition_penalty=c.penalties[i]))
+        got = sched._sample_next_ids(c.logits.cuda(), reqs, c.mode)
+        assert torch.equal(got.cpu(), c.next_ids), name
+        assert FakeScheduler.calls == 0
+    reqs[0].do_sample = True
+    assert int(sched._sample_next_ids(c.logits.cuda(), reqs, c.mode)[0]) == -7 and FakeScheduler.calls == 1

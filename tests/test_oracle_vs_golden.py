@@ -108,3 +108,11 @@ def test_rope_matches_reference_bit_for_bit(name):
     assert torch.equal(k_slab[loc.long()].view(torch.int16), g.k_rot.view(torch.int16))
     assert torch.equal(v_slab[loc.long()], v.reshape(T, g.Hkv, g.D))
     assert k_slab[0].abs().sum() == 0
+
+
+def test_greedy_sample_matches_reference_scheduler():
+    """oracle.greedy_sample vs the ids the reference's Scheduler._sample_next_ids returned."""
+    from tests.helpers import load_sample_golden
+    for name, c in load_sample_golden().items():
+        got = O.greedy_sample(c.logits, c.extended_lens if c.mode == "prefill" else None, c.prev_ids, c.penalties)
+        assert torch.equal(got, c.next_ids), name
