@@ -31,6 +31,20 @@
 
 namespace bsgl {
 
+// Development aid (scripts/ext_trace.cu): per-role clock64 timestamps of one CTA.  Compiled out of the library.
+#ifdef BSGL_EXT_TRACE
+__device__ long long* g_ext_trace = nullptr;   // [role 10][step 128][event 8]; roles: softmax warps 0-7, MMA 8, producer 9
+__device__ int g_ext_trace_cta = 0;
+#define BSGL_TR_INIT() long long* const tr_base = (blockIdx.x == g_ext_trace_cta) ? g_ext_trace : nullptr
+#define BSGL_TR(role, step, ev)                                                              \
+  do {                                                                                       \
+    if (tr_base && (step) < 128) tr_base[((role) * 128 + (step)) * 8 + (ev)] = clock64();    \
+  } while (0)
+#else
+#define BSGL_TR_INIT() do {} while (0)
+#define BSGL_TR(role, step, ev) do {} while (0)
+#endif
+
 constexpr int kExtSoftmaxWarps = 8;
 constexpr int kExtMmaWarp = 8;
 constexpr int kExtProducerWarps = 3;
@@ -80,6 +94,7 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
   if (smem_base & 1023u) __trap();
   uint8_t* smem = smem_raw;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  BSGL_TR_INIT();
   const int G = n_q_heads / n_kv_heads;
   const int TQ = kExtRows / G;                // tokens per chunk
   const int h = blockIdx.x % n_kv_heads;      // KV head: fastest, so the heads of one chunk run together
@@ -160,7 +175,9 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
     const int tok = m / G;
     const int head = m - tok * G;
     const bool valid = tok < n_tok && m < TQ * G;
-    const int limit = valid ? prefix + t0 + tok : -1;      // last visible KV column
+    // last visible KV column.  Padding rows (zero-filled Q, never stored) see everything: a row that
+    // masked every tile would drag its whole warp through the mask code on every tile.
+    const int limit = valid ? prefix + t0 + tok : 0x3fffffff;
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t s_addr = tmem + lane_base + x * 128;
     const uint32_t o_addr = tmem + lane_base + C::O_COL + x * D;
@@ -169,10 +186,12 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
     for (int j = 0; j < nkv; ++j) {
       mbar_wait_guarded(s_full + 8 * x, j & 1);
       tc::fence_after_sync();
+      if (lane == 0) BSGL_TR(warp, j, 0);
       uint32_t s[4][32];
 #pragma unroll
       for (int c = 0; c < 4; ++c) tc::ld32(s_addr + c * 32, s[c]);
       tc::wait_ld();
+      if (lane == 0) BSGL_TR(warp, j, 1);
       const int nvalid = limit - j * kExtKvTile + 1;       // visible columns of this tile
       if (nvalid < kExtKvTile) {
 #pragma unroll
@@ -181,19 +200,74 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
           for (int i = 0; i < 32; ++i)
             if (c * 32 + i >= nvalid) s[c][i] = 0xff800000u;   // -inf
       }
-      float mxs[8];
+      // Exponentials of P column group c under the reference max -neg_m (base 2), packed to 16-bit pairs.
+      constexpr int NP = 64 / kExtPParts;                 // packed P columns per group
+      auto exp_group = [&](int c, float neg_m, uint32_t (&p)[NP], uint64_t (&sums)[2], float (&mxs)[4], bool with_max) {
+        const uint64_t scale2 = pack_f32x2(scale_log2, scale_log2), negm2 = pack_f32x2(neg_m, neg_m);
+        // Software pipeline: the exponentials of batch b+1 are issued before batch b is summed and packed,
+        // so 2 * BP SFU results are in flight and their latency is covered (the consumer of an ex2 placed
+        // right behind it would stall the warp for the SFU latency on every pair).
+        constexpr int BP = 8, NB = NP / BP;
+        float e0[2][BP], e1[2][BP];
+        auto issue = [&](int bt, int buf) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
-        mxs[i] = fmaxf(fmaxf(__uint_as_float(s[0][i]), __uint_as_float(s[1][i])),
-                       fmaxf(__uint_as_float(s[2][i]), __uint_as_float(s[3][i])));
+          for (int k = 0; k < BP; ++k) {
+            const int i = bt * BP + k;
+            const int e = c * 2 * NP + 2 * i;          // adjacent columns = adjacent registers = one FFMA2
+            const uint64_t x2 = ffma2(pack_f32x2(__uint_as_float(s[e >> 5][e & 31]), __uint_as_float(s[e >> 5][(e & 31) + 1])),
+                                      scale2, negm2);
+            // EXPMODE: share of the exponential PAIRS evaluated on the FMA pipe instead of the SFU
+            //   0 none, 1 one in four, 2 two in four, 3 three in four; 4/5/6 = timing experiments only
+            const bool poly = (EXPMODE == 1 && (i & 3) == 3) || (EXPMODE == 2 && (i & 1) == 1) || (EXPMODE == 3 && (i & 3) != 0);
+            if (EXPMODE == 4 || EXPMODE == 6) {
+              unpack_f32x2(x2, e0[buf][k], e1[buf][k]);
+            } else if (poly) {
+              poly_exp2_x2(x2, e0[buf][k], e1[buf][k]);
+            } else {
+              float x0, x1;
+              unpack_f32x2(x2, x0, x1);
+              e0[buf][k] = fast_exp2_ordered(x0);
+              e1[buf][k] = fast_exp2_ordered(x1);
+            }
+          }
+        };
+        auto retire = [&](int bt, int buf) {
 #pragma unroll
-      for (int i = 8; i < 32; ++i)
-        mxs[i & 7] = fmaxf(mxs[i & 7], fmaxf(fmaxf(__uint_as_float(s[0][i]), __uint_as_float(s[1][i])),
-                                             fmaxf(__uint_as_float(s[2][i]), __uint_as_float(s[3][i]))));
-      const float mx = fmaxf(fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])),
-                             fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
+          for (int k = 0; k < BP; ++k) {
+            const int i = bt * BP + k;
+            sums[i & 1] = fadd2_ordered(sums[i & 1], pack_f32x2(e0[buf][k], e1[buf][k]));
+            p[i] = pack2<T>(e0[buf][k], e1[buf][k]);
+            if (with_max) {
+              // the tile's row max rides along in the issue slots the SFU-bound exponentials leave free:
+              // 128 / NP columns per pair
+              constexpr int MPI = 128 / NP;
+#pragma unroll
+              for (int t = 0; t < MPI; ++t) {
+                const int col = i * MPI + t;
+                mxs[t & 3] = fmaxf(mxs[t & 3], __uint_as_float(s[col >> 5][col & 31]));
+              }
+            }
+          }
+        };
+        issue(0, 0);
+#pragma unroll
+        for (int bt = 0; bt < NB; ++bt) {
+          if (bt + 1 < NB) issue(bt + 1, (bt + 1) & 1);
+          retire(bt, bt & 1);
+        }
+      };
+      // Group 0 is evaluated speculatively under the running reference max while the tile max is still
+      // being reduced; only if the max grew past the lazy-rescale threshold (first tile, rare later) is it
+      // redone after the rescale.  Results are identical to max-then-exp; the max pass leaves the critical path.
+      float neg_m = (m_used == -INFINITY) ? 0.f : -m_used;
+      uint64_t sums[2] = {0ull, 0ull};                    // two packed fp32 pairs (+0.0f bit patterns)
+      float mxs[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      uint32_t p[NP];
+      exp_group(0, neg_m, p, sums, mxs, true);
+      const float mx = fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3]));
       const float m_new = fmaxf(m_used, mx * scale_log2);
       const bool grow = (m_new - m_used) > kRescaleThreshold;   // false for NaN (-inf - -inf)
+      if (lane == 0) BSGL_TR(warp, j, 2);
       if (__any_sync(0xffffffffu, grow)) {
         const float alpha = (m_new == -INFINITY) ? 1.f : fast_exp2(m_used - m_new);
         l *= alpha;
@@ -209,35 +283,26 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
             tc::st32(o_addr + c * 32, o);
           }
         }
+        neg_m = (m_used == -INFINITY) ? 0.f : -m_used;
+        sums[0] = sums[1] = 0ull;
+        exp_group(0, neg_m, p, sums, mxs, false);
       }
-      const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used;
-      float sums[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int c = 0; c < kExtPParts; ++c) {
-        constexpr int NP = 64 / kExtPParts;               // packed P columns per group
-        uint32_t p[NP];
-#pragma unroll
-        for (int i = 0; i < NP; ++i) {
-          const int e = c * 2 * NP + 2 * i;
-          const float x0 = fmaf(__uint_as_float(s[e >> 5][e & 31]), scale_log2, neg_m);
-          const float x1 = fmaf(__uint_as_float(s[(e + 1) >> 5][(e + 1) & 31]), scale_log2, neg_m);
-          // EXPMODE: share of the exponentials evaluated on the FMA pipe instead of the SFU
-          //   0 none, 1 one in four, 2 one in two, 3 all; 4/5/6 = timing experiments only
-          const bool poly0 = EXPMODE == 3 || (EXPMODE == 2) || (EXPMODE == 1 && (i & 1) == 0);
-          const bool poly1 = EXPMODE == 3;
-          const float p0 = (EXPMODE == 4 || EXPMODE == 6) ? x0 : (poly0 ? poly_exp2(x0) : fast_exp2(x0));
-          const float p1 = (EXPMODE == 4 || EXPMODE == 6) ? x1 : (poly1 ? poly_exp2(x1) : fast_exp2(x1));
-          sums[i & 3] += p0 + p1;
-          p[i] = pack2<T>(p0, p1);
-        }
+        if (c > 0) exp_group(c, neg_m, p, sums, mxs, false);
         tc::st_cols(s_addr + c * NP, p);
         // hand each column group of P to the MMA warp as soon as it is stored: PV_X of the earlier
         // groups runs under the later groups' exponentials
         tc::wait_st();
         tc::fence_before_sync();
         mbar_arrive(p_full + 16 * c + 8 * x);
+        if (lane == 0) BSGL_TR(warp, j, 3 + c);
       }
-      l += (sums[0] + sums[1]) + (sums[2] + sums[3]);
+      {
+        float a0, a1;
+        unpack_f32x2(fadd2(sums[0], sums[1]), a0, a1);
+        l += a0 + a1;
+      }
     }
     // ---- epilogue: O / l -> out[token, head, :]
     mbar_wait_guarded(s_full + 8 * x, nkv & 1);
@@ -314,17 +379,20 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
       for (int j = 0; j < nkv; ++j) {
         const int uv = 2 * j + 1, uk = 2 * j + 2;     // V_j, K_{j+1}
         wait_tile(uv);
+        if (lane == 0) BSGL_TR(8, j, 0);
 #pragma unroll
         for (int x = 0; x < 2; ++x) {
 #pragma unroll
           for (int hlf = 0; hlf < kExtPParts; ++hlf) {
             mbar_wait_guarded(p_full + 16 * hlf + 8 * x, j & 1);
             tc::fence_after_sync();
+            if (lane == 0) BSGL_TR(8, j, 1 + 3 * x + hlf);
             issue_pv(x, uv, hlf, j > 0, x == 1, j + 1 >= nkv);
           }
           if (j + 1 < nkv) {
             if (x == 0) wait_tile(uk);
             issue_s(x, uk, x == 1);
+            if (lane == 0) BSGL_TR(8, j, 3 + 3 * x);
           }
         }
       }
@@ -369,6 +437,7 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
         const int u = 2 * j + kv;
         const int slot = u % RING;
         mbar_wait_guarded(empty0 + 8 * slot, ((u / RING) & 1) ^ 1);
+        if (p == 0) BSGL_TR(9, j, 2 * kv);
         const T* base = kv == 0 ? kb : vb;
         const uint32_t dst = ring_smem + slot * C::TILE_BYTES;
 #pragma unroll
@@ -380,6 +449,7 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
           }
         }
         cp_async_mbar_arrive(full0 + 8 * slot);      // arrives when this thread's copies have landed
+        if (p == 0) BSGL_TR(9, j, 2 * kv + 1);
       }
     }
     cp_async_wait_all();                             // nothing of this CTA is in flight at exit

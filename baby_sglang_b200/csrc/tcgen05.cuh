@@ -175,11 +175,85 @@ __device__ __forceinline__ float poly_exp2(float x) {
 }
 
 // mbarrier wait that traps instead of hanging the GPU if the pipeline protocol is ever violated.
+// The suspend-time hint lets the hardware park the warp until the phase completes (or the hint
+// expires) instead of returning at once: a waiting role then issues a handful of instructions per
+// wait, not a spin loop that competes for the issue port with the working warps of its SMSP.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint32_t bar, uint32_t parity, uint32_t hint_ns) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity), "r"(hint_ns)
+      : "memory");
+  return ok != 0;
+}
 __device__ __forceinline__ void mbar_wait_guarded(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 19)) __trap();   // try_wait suspends ~microseconds per try: about a second
+  while (!mbar_try_wait_hint(bar, parity, 100000u)) {
+    if (++spins > (1u << 16)) __trap();   // seconds: only a protocol bug gets here
   }
+}
+
+// ---------------------------------------------------------------- packed fp32 pairs (FFMA2 / FADD2)
+// Blackwell issues two fp32 FMAs per lane per instruction on 64-bit register pairs; adjacent S
+// columns arrive from tcgen05.ld in adjacent registers, so the pairs cost no moves.
+__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// `volatile` keeps the source order of the software-pipelined exponential loop (issue batch b+1, then
+// retire batch b) through the compiler's scheduler.
+__device__ __forceinline__ uint64_t fadd2_ordered(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm volatile("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ float fast_exp2_ordered(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ uint64_t fadd2_rm(uint64_t a, uint64_t b) {   // round toward -inf
+  uint64_t d;
+  asm("add.rm.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+// Two 2^x on the FMA pipe (packed form of poly_exp2): x = floor(x) + r, degree-3 minimax for 2^r,
+// floor(x) added into the exponent field.  Inputs are clamped to >= -126 (2^-126 instead of 0).
+__device__ __forceinline__ void poly_exp2_x2(uint64_t x2, float& p0, float& p1) {
+  float x0, x1;
+  unpack_f32x2(x2, x0, x1);
+  x2 = pack_f32x2(fmaxf(x0, -126.f), fmaxf(x1, -126.f));
+  const uint64_t magic = pack_f32x2(12582912.f, 12582912.f);   // 1.5 * 2^23
+  const uint64_t t2 = fadd2_rm(x2, magic);                     // magic + floor(x)
+  const uint64_t f2 = fadd2(t2, pack_f32x2(-12582912.f, -12582912.f));
+  const uint64_t r2 = ffma2(f2, pack_f32x2(-1.f, -1.f), x2);   // x - floor(x) in [0, 1)
+  uint64_t q2 = ffma2(pack_f32x2(0.077119089663028717f, 0.077119089663028717f), r2,
+                      pack_f32x2(0.227564394474029541f, 0.227564394474029541f));
+  q2 = ffma2(q2, r2, pack_f32x2(0.695146143436431885f, 0.695146143436431885f));
+  q2 = ffma2(q2, r2, pack_f32x2(1.f, 1.f));
+  float q0, q1, t0, t1;
+  unpack_f32x2(q2, q0, q1);
+  unpack_f32x2(t2, t0, t1);
+  p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+  p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
 }
 
 }  // namespace bsgl
