@@ -20,8 +20,13 @@
 //                        overlaps the other tile's MMAs; tcgen05.commit signals the mbarriers.
 //   softmax (2 x 4 warps) one thread per row: tcgen05.ld the S row, mask `col <= prefix + token`,
 //                        online softmax in base 2 with lazy rescaling of O (only when the running
-//                        max grows by > 2^8), P written back over S as packed 16-bit pairs
-//                        (tcgen05.st), final O / l -> out.
+//                        max grows by > 2^8).  The first half's exponentials are evaluated under the
+//                        running max while the tile max is still being reduced (redone only when the
+//                        max grew past the threshold), so the max pass is off the critical path; math is
+//                        packed fp32x2 (FFMA2/FADD2); one pair in four of the second half goes through a
+//                        polynomial on the FMA pipe instead of the SFU.  P is written back over S as
+//                        packed 16-bit pairs (tcgen05.st) and handed over in two halves; final O / l -> out.
+//                        Padding rows (beyond the chunk's tokens) are never masked and never stored.
 //
 // TMEM columns: S_A [0,128) S_B [128,256) O_A [256,256+D) O_B [256+D,256+2D); P_X aliases S_X.
 // Tensor-bound: flops = 4 * Hq * D * sum_i ext_i * (prefix_i + (ext_i + 1) / 2).
@@ -218,7 +223,10 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
                                       scale2, negm2);
             // EXPMODE: share of the exponential PAIRS evaluated on the FMA pipe instead of the SFU
             //   0 none, 1 one in four, 2 two in four, 3 three in four; 4/5/6 = timing experiments only
-            const bool poly = (EXPMODE == 1 && (i & 3) == 3) || (EXPMODE == 2 && (i & 1) == 1) || (EXPMODE == 3 && (i & 3) != 0);
+            // (only in the later column groups: the first group runs with all 128 S values live and has no
+            // registers to spare for the polynomial's temporaries)
+            const bool poly = c > 0 && ((EXPMODE == 1 && (i & 3) == 3) || (EXPMODE == 2 && (i & 1) == 1) ||
+                                        (EXPMODE == 3 && (i & 3) != 0));
             if (EXPMODE == 4 || EXPMODE == 6) {
               unpack_f32x2(x2, e0[buf][k], e1[buf][k]);
             } else if (poly) {
@@ -520,21 +528,21 @@ extern "C" int bsgl_extend_attention(const void* q, const void* k_slab, const vo
                "bsgl_extend_attention: pointers must be 16-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
   static const int expmode = [] {
-    const char* e = getenv("BSGL_EXT_EXPMODE");
-    return e ? atoi(e) : 0;
+    const char* e = getenv("BSGL_EXT_EXPMODE");   // development knob; default = measured best (1)
+    return e ? atoi(e) : 1;
   }();
 #define BSGL_EXT1(T, D, M)                                                                                          \
   return launch_extend<T, D, M>(q, k_slab, v_slab, req_to_token, page_table_stride, req_pool_indices, prefix_lens, \
                                 qo_indptr, req_order, batch, n_tokens, n_q_heads, n_kv_heads, sm_scale, out, s)
 #define BSGL_EXT(T, D)                    \
   do {                                    \
-    if (expmode == 1) BSGL_EXT1(T, D, 1); \
+    if (expmode == 0) BSGL_EXT1(T, D, 0); \
     if (expmode == 2) BSGL_EXT1(T, D, 2); \
     if (expmode == 3) BSGL_EXT1(T, D, 3); \
     if (expmode == 4) BSGL_EXT1(T, D, 4); \
     if (expmode == 5) BSGL_EXT1(T, D, 5); \
     if (expmode == 6) BSGL_EXT1(T, D, 6); \
-    BSGL_EXT1(T, D, 0);                   \
+    BSGL_EXT1(T, D, 1);                   \
   } while (0)
   if (dtype == BSGL_BF16) {
     if (head_dim == 128) BSGL_EXT(__nv_bfloat16, 128);
