@@ -3,7 +3,7 @@ attributes; reference memory_pool.py:7-171), backed by B200 kernels where the re
 torch index-puts.
 
     ReqToTokenPool      page table `req_to_token` int32 [max_reqs, max_context_len] + FIFO of rows
-    BaseTokenToKVPool   FIFO of KV slots 1..size on the host (slot 0 is the pad slot)
+    BaseTokenToKVPool   FIFO of KV slots 1..size (slot 0 is the pad slot); a device ring on CUDA pools (K7)
     MHATokenToKVPool    per-layer K / V slabs [size+1, H, D]; set_kv_buffer -> K1 (bsgl_kv_store)
 
 Allocation ORDER is part of the contract (KV-slot indexing must be bit-exact with the reference):
@@ -12,6 +12,7 @@ de-duplication (memory_pool.py:29-41, 68-84).
 """
 from __future__ import annotations
 
+import os
 from collections import deque
 from typing import Deque, List, Optional, Tuple, Union
 
@@ -56,35 +57,46 @@ class ReqToTokenPool:
 
 
 class BaseTokenToKVPool:
-    """Host-side FIFO of free KV slots.  Kept as a growable int32 ring so `alloc`/`free` are O(n)
-    in the slots moved rather than in the pool size; `free_slots` materialises the queue in order
-    (a CPU int32 tensor, like the reference attribute)."""
+    """FIFO of free KV slots, order identical to the reference's (head out, tail in; memory_pool.py:68-84).
+
+    On a CUDA pool the queue is a ring in device memory (K7): `alloc` is one stream-ordered pop kernel instead of
+    a CPU slice + H2D copy, `free` one push kernel that reads the freed slots where they are (usually a slice of
+    a page-table row) instead of the reference's blocking `.cpu()` (memory_pool.py:77).  Head and count stay on
+    the host: every size is known there.  On a CPU pool (host-logic tests) the ring is a CPU tensor.
+    `free_slots` materialises the queue in order as a CPU int32 tensor, like the reference attribute."""
 
     def __init__(self, size: int, dtype: torch.dtype, device: str):
         self.size = size
         self.dtype = dtype
         self.store_dtype = torch.uint8 if dtype in _FP8 else dtype
         self.device = device
+        self._dev_ring = torch.device(device).type == "cuda" and os.environ.get("BSGL_DEVICE_SLOT_RING", "1") != "0"
         self._ring: torch.Tensor = None
         self._head = 0
         self._count = 0
         self.clear()
 
     # -- queue plumbing ------------------------------------------------------------------
-    def _grow(self, need: int) -> None:
-        cap = int(self._ring.numel())
-        new_cap = max(2 * cap, self._count + need)
-        fresh = torch.empty(new_cap, dtype=torch.int32)
-        fresh[: self._count] = self.free_slots
-        self._ring, self._head = fresh, 0
-
-    @property
-    def free_slots(self) -> torch.Tensor:
+    def _ordered(self) -> torch.Tensor:
+        """The queue contents in FIFO order, on the ring's device."""
+        if self._dev_ring:
+            return ops.slot_ring_pop(self._ring, self._head, self._count)
         cap = int(self._ring.numel())
         end = self._head + self._count
         if end <= cap:
             return self._ring[self._head:end]
         return torch.cat((self._ring[self._head:], self._ring[: end - cap]))
+
+    def _grow(self, need: int) -> None:
+        cap = int(self._ring.numel())
+        new_cap = max(2 * cap, self._count + need)
+        fresh = torch.empty(new_cap, dtype=torch.int32, device=self._ring.device)
+        fresh[: self._count] = self._ordered()
+        self._ring, self._head = fresh, 0
+
+    @property
+    def free_slots(self) -> torch.Tensor:
+        return self._ordered().cpu()
 
     # -- reference API -------------------------------------------------------------------
     def available_size(self) -> int:
@@ -95,32 +107,42 @@ class BaseTokenToKVPool:
             return None
         cap = int(self._ring.numel())
         end = self._head + need_size
-        if end <= cap:
+        if self._dev_ring:
+            picked = ops.slot_ring_pop(self._ring, self._head, need_size)
+        elif end <= cap:
             picked = self._ring[self._head:end].clone()
         else:
             picked = torch.cat((self._ring[self._head:], self._ring[: end - cap]))
         self._head = end % cap
         self._count -= need_size
-        return picked.to(self.device, non_blocking=True)
+        return picked if self._dev_ring else picked.to(self.device, non_blocking=True)
 
     def free(self, free_index: torch.Tensor) -> None:
         n = int(free_index.numel())
         if n == 0:
             return
-        vals = free_index.detach().to("cpu", torch.int32).reshape(-1)
         if self._count + n > int(self._ring.numel()):
             self._grow(n)
         cap = int(self._ring.numel())
         tail = (self._head + self._count) % cap
-        first = min(n, cap - tail)
-        self._ring[tail:tail + first] = vals[:first]
-        if first < n:
-            self._ring[: n - first] = vals[first:]
+        if self._dev_ring:
+            vals = free_index.detach()
+            if not vals.is_cuda:
+                vals = vals.to(self._ring.device, non_blocking=True)
+            if vals.dtype not in (torch.int32, torch.int64):
+                vals = vals.to(torch.int64)
+            ops.slot_ring_push(self._ring, tail, vals.reshape(-1) if vals.dim() != 1 else vals)
+        else:
+            vals = free_index.detach().to("cpu", torch.int32).reshape(-1)
+            first = min(n, cap - tail)
+            self._ring[tail:tail + first] = vals[:first]
+            if first < n:
+                self._ring[: n - first] = vals[first:]
         self._count += n
 
     def clear(self) -> None:
         # slots 1..size; slot 0 is reserved for padded tokens' dummy writes
-        self._ring = torch.arange(1, self.size + 1, dtype=torch.int32)
+        self._ring = torch.arange(1, self.size + 1, dtype=torch.int32, device=self.device if self._dev_ring else "cpu")
         self._head = 0
         self._count = self.size
 

@@ -125,3 +125,110 @@ def install_batched_greedy_sampler(scheduler) -> None:
     if not hasattr(type(scheduler), "_sample_next_ids"):
         raise ValueError("object has no _sample_next_ids method (scheduler.py:509)")
     scheduler._sample_next_ids = types.MethodType(_batched_sample_next_ids, scheduler)
+
+
+# ------------------------------------------------------------------------------------------------------
+# around the path: device-side page-table update
+# ------------------------------------------------------------------------------------------------------
+def _device_prepare_prefill_batch(self, batch_requests):
+    """Drop-in for Scheduler._prepare_prefill_batch (scheduler.py:381-452).  Same allocations in the same
+    order, same errors, same request bookkeeping and the same page-table rows ([reused prefix slots |
+    new slots | 0 ...] over all C cells), but: one H2D copy of a packed [5, B] descriptor instead of three
+    `torch.tensor` uploads, one K7 launch instead of `zeros([B, C])` + two slice writes per request + a
+    whole-row index-put, and no `.item()` (the reference syncs once per request at :439)."""
+    import forward_batch as fb_mod   # the drop-in module (first on sys.path wherever the reference stack runs)
+
+    B = len(batch_requests)
+    rows = self.req_to_token_pool.alloc(B)
+    if rows is None:
+        raise RuntimeError("Failed to allocate request pool indices")
+    seq_lens = [len(req.input_ids) for req in batch_requests]
+    prefix_lens = [int(req.num_cached_tokens) for req in batch_requests]
+    concat_input_ids = torch.cat([req.input_ids[req.num_cached_tokens:] for req in batch_requests], dim=0)
+    total_tokens = int(concat_input_ids.shape[0])
+
+    out_cache_loc = self.token_to_kv_pool.alloc(total_tokens)
+    if out_cache_loc is None:
+        # need eviction from the radix cache (scheduler.py:410-421)
+        self.tree_cache.evict(total_tokens, self.token_to_kv_pool.free)
+        out_cache_loc = self.token_to_kv_pool.alloc(total_tokens)
+        if out_cache_loc is None:
+            avail = self.token_to_kv_pool.available_size() + self.tree_cache.evictable_size()
+            raise RuntimeError(f"Prefill OOM: need {total_tokens}, available {avail}")
+
+    new_offs, prefix_offs, n_new, n_pre = [], [], 0, 0
+    for s, p in zip(seq_lens, prefix_lens):
+        new_offs.append(n_new)
+        prefix_offs.append(n_pre)
+        n_new += s - p
+        n_pre += p
+    desc = torch.tensor([list(rows), prefix_lens, seq_lens, new_offs, prefix_offs], dtype=torch.int64)
+    desc = desc.to(self.device, non_blocking=True)
+    pool = self.req_to_token_pool
+    prefix_flat = None
+    if n_pre:
+        parts = []
+        for req, p in zip(batch_requests, prefix_lens):
+            if p:
+                if int(req.prefix_indices.shape[0]) != p:   # the reference's slice assignment would raise (:434)
+                    raise RuntimeError(f"prefix_indices has {int(req.prefix_indices.shape[0])} slots, expected {p}")
+                parts.append(req.prefix_indices)
+        prefix_flat = torch.cat(parts).to(device=pool.req_to_token.device, dtype=torch.int32).contiguous()
+    ops.page_table_write_rows(pool.req_to_token, desc, prefix_flat, out_cache_loc)
+
+    for req, row, s in zip(batch_requests, rows, seq_lens):
+        req.req_pool_idx = int(row)
+        req.seq_len = s
+
+    return fb_mod.SimplifiedForwardBatch.create_prefill_batch(
+        input_ids=concat_input_ids, req_pool_indices=desc[0], seq_lens=desc[2], out_cache_loc=out_cache_loc,
+        req_to_token_pool=pool, token_to_kv_pool=self.token_to_kv_pool, prefix_lens=desc[1])
+
+
+def _device_prepare_decode_batch(self, batch_requests):
+    """Drop-in for Scheduler._prepare_decode_batch (scheduler.py:454-507): the B scalar device writes
+    `req_to_token[r, seq_len] = slot` (:486-488) become one K7 launch and the three uploads one."""
+    import forward_batch as fb_mod
+
+    B = len(batch_requests)
+    new_kv_slots = self.token_to_kv_pool.alloc(B)
+    if new_kv_slots is None:
+        raise RuntimeError("Failed to allocate KV slots for decode")
+    rows, ids, lens = [], [], []
+    for i, req in enumerate(batch_requests):
+        if req.req_pool_idx is None:
+            raise RuntimeError(f"Request {i} missing req_pool_idx for decode")
+        if req.is_retracted:
+            raise RuntimeError(f"Request {i} was retracted but is scheduled for decode")
+        rows.append(req.req_pool_idx)
+        # the last generated token is the input (a negative placeholder in overlap mode, overlap_worker.py:74-81)
+        if req.overlap_next_input_id is not None:
+            ids.append(req.overlap_next_input_id)
+        else:
+            if not req.output_ids:
+                raise RuntimeError(f"Request {i} has no output tokens for decode")
+            ids.append(req.output_ids[-1])
+        lens.append(req.seq_len + 1)
+    for req in batch_requests:          # only after every check passed, like the reference's single loop would
+        req.seq_len += 1
+    packed = torch.tensor([rows, lens, ids], dtype=torch.int64).to(self.device, non_blocking=True)
+    pool = self.req_to_token_pool
+    ops.page_table_append(pool.req_to_token, packed[0], packed[1], new_kv_slots)
+    return fb_mod.SimplifiedForwardBatch.create_decode_batch(
+        input_ids=packed[2], req_pool_indices=packed[0], seq_lens=packed[1], out_cache_loc=new_kv_slots,
+        req_to_token_pool=pool, token_to_kv_pool=self.token_to_kv_pool)
+
+
+def install_device_batch_prep(scheduler) -> None:
+    """Route `_prepare_prefill_batch` / `_prepare_decode_batch` of an instance of the reference's unchanged
+    Scheduler through K7.  `_prepare_forward` (scheduler.py:371-379) dispatches to the instance attributes."""
+    for name in ("_prepare_prefill_batch", "_prepare_decode_batch"):
+        if not hasattr(type(scheduler), name):
+            raise ValueError(f"object has no {name} method (scheduler.py:381,454)")
+    scheduler._prepare_prefill_batch = types.MethodType(_device_prepare_prefill_batch, scheduler)
+    scheduler._prepare_decode_batch = types.MethodType(_device_prepare_decode_batch, scheduler)
+
+
+def uninstall_device_batch_prep(scheduler) -> None:
+    for name in ("_prepare_prefill_batch", "_prepare_decode_batch"):
+        scheduler.__dict__.pop(name, None)

@@ -438,3 +438,83 @@ def greedy_sample(logits: torch.Tensor, qo_indptr: Optional[torch.Tensor] = None
     _lib.check(rc, "bsgl_greedy_sample")
     _count()
     return out
+
+
+# --------------------------------------------------------------------------------------- K7
+def _check_page_table(req_to_token: torch.Tensor) -> None:
+    if req_to_token.dtype != torch.int32 or req_to_token.dim() != 2 or req_to_token.stride(1) != 1:
+        raise _lib.BsglError("req_to_token must be an int32 [rows, C] table with unit inner stride")
+
+
+def page_table_write_rows(req_to_token: torch.Tensor, desc: torch.Tensor, prefix_flat: Optional[torch.Tensor],
+                          new_slots: Optional[torch.Tensor]) -> None:
+    """Prefill rows of one batch in one launch (reference scheduler.py:423-442).  `desc` is int64
+    [5, B]: req_pool_idx, prefix_len, seq_len, new_off, prefix_off; row r becomes
+    [prefix_flat[prefix_off:+prefix] | new_slots[new_off:+seq-prefix] | zeros] over all C cells."""
+    _require_cuda(req_to_token, desc, prefix_flat, new_slots)
+    _check_page_table(req_to_token)
+    if desc.dtype != torch.int64 or desc.dim() != 2 or desc.shape[0] != 5 or not desc.is_contiguous():
+        raise _lib.BsglError("desc must be a contiguous int64 [5, B] tensor")
+    for name, t in (("prefix_flat", prefix_flat), ("new_slots", new_slots)):
+        if t is not None and (t.dtype != torch.int32 or not t.is_contiguous()):
+            raise _lib.BsglError(f"{name} must be contiguous int32")
+    B = int(desc.shape[1])
+    if B == 0:
+        return
+    null = ctypes.c_void_p(0)
+    rc = _lib.load().bsgl_page_table_write_rows(
+        req_to_token.data_ptr(), req_to_token.stride(0), int(req_to_token.shape[0]), int(req_to_token.shape[1]),
+        desc.data_ptr(), B, prefix_flat.data_ptr() if prefix_flat is not None and prefix_flat.numel() else null,
+        new_slots.data_ptr() if new_slots is not None and new_slots.numel() else null, _stream())
+    _lib.check(rc, "bsgl_page_table_write_rows")
+    _count()
+
+
+def page_table_append(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
+                      slots: torch.Tensor) -> None:
+    """`req_to_token[req_pool_indices[i], seq_lens[i] - 1] = slots[i]` for the whole decode batch in one
+    launch (reference scheduler.py:486-488; `seq_lens` already counts the new token, :489-490)."""
+    _require_cuda(req_to_token, req_pool_indices, seq_lens, slots)
+    _check_page_table(req_to_token)
+    if req_pool_indices.dtype != torch.int64 or seq_lens.dtype != torch.int64 or slots.dtype != torch.int32:
+        raise _lib.BsglError("req_pool_indices / seq_lens must be int64 and slots int32")
+    B = int(slots.shape[0])
+    if int(req_pool_indices.shape[0]) != B or int(seq_lens.shape[0]) != B:
+        raise _lib.BsglError("req_pool_indices / seq_lens / slots lengths differ")
+    if B == 0:
+        return
+    rc = _lib.load().bsgl_page_table_append(
+        req_to_token.data_ptr(), req_to_token.stride(0), int(req_to_token.shape[0]), int(req_to_token.shape[1]),
+        req_pool_indices.contiguous().data_ptr(), seq_lens.contiguous().data_ptr(), slots.contiguous().data_ptr(), B,
+        _stream())
+    _lib.check(rc, "bsgl_page_table_append")
+    _count()
+
+
+def slot_ring_pop(ring: torch.Tensor, head: int, n: int) -> torch.Tensor:
+    """n slots from the head of the device FIFO `ring` (int32 [capacity]) in FIFO order (memory_pool.py:68-74)."""
+    dev = _require_cuda(ring)
+    out = torch.empty(n, dtype=torch.int32, device=dev)
+    if n:
+        rc = _lib.load().bsgl_slot_ring_pop(ring.data_ptr(), int(ring.numel()), int(head), int(n), out.data_ptr(),
+                                            _stream())
+        _lib.check(rc, "bsgl_slot_ring_pop")
+        _count()
+    return out
+
+
+def slot_ring_push(ring: torch.Tensor, tail: int, vals: torch.Tensor) -> None:
+    """Append `vals` (int32/int64 device tensor, any 1-D stride, e.g. a slice of a page-table row) at the
+    tail of the device FIFO, in order, without a device->host copy (memory_pool.py:76-80)."""
+    _require_cuda(ring, vals)
+    if vals.dtype not in (torch.int32, torch.int64):
+        raise _lib.BsglError(f"freed slots must be int32 or int64, got {vals.dtype}")
+    if vals.dim() != 1:
+        vals = vals.reshape(-1)
+    n = int(vals.numel())
+    if n == 0:
+        return
+    rc = _lib.load().bsgl_slot_ring_push(ring.data_ptr(), int(ring.numel()), int(tail), n, vals.data_ptr(),
+                                         int(vals.stride(0)), 1 if vals.dtype == torch.int64 else 0, _stream())
+    _lib.check(rc, "bsgl_slot_ring_push")
+    _count()

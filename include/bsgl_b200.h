@@ -23,6 +23,9 @@
  *   bsgl_extend_attention       _prefill_attention                         attn_backend.py:34-110
  *   bsgl_rope_kv_store          RotaryEmbedding.forward + split + set_kv_buffer qwen2.py:249-290
  *   bsgl_greedy_sample          Scheduler._sample_next_ids (greedy requests)   scheduler.py:509-546, sample.py:19-60
+ *   bsgl_page_table_write_rows  prefill page-table rows                    scheduler.py:423-442
+ *   bsgl_page_table_append      decode page-table cells                    scheduler.py:486-488
+ *   bsgl_slot_ring_pop / _push  BaseTokenToKVPool.alloc / free             memory_pool.py:68-80
  *
  * Layout conventions (identical to the reference's tensors):
  *   q        [rows, n_q_heads, head_dim]            contiguous, bf16 or fp16
@@ -180,6 +183,34 @@ int bsgl_greedy_sample(const void* logits, int64_t row_stride, int vocab, int dt
                        const int32_t* qo_indptr, int batch, const int64_t* prev_ids,
                        const int32_t* prev_indptr, const float* penalties, int64_t* next_ids,
                        void* stream);
+
+/* K7 (device-side page-table update + slot allocator).  Integer, bit-exact.
+ *
+ * bsgl_page_table_write_rows: the prefill rows of one batch in one launch (scheduler.py:423-442:
+ * zeros([B, C]) + per-request slice writes + whole-row index-put).  Row desc[0][i] of the table
+ * becomes [prefix_flat[prefix_off .. +prefix) | new_slots[new_off .. +seq-prefix) | 0 ...] over
+ * row_len cells.  desc is int64 [5][batch]: req_pool_idx, prefix_len, seq_len, new_off, prefix_off.
+ * prefix_flat / new_slots may be NULL when no request reads them. */
+int bsgl_page_table_write_rows(int32_t* req_to_token, int64_t page_table_stride, int64_t n_rows,
+                               int row_len, const int64_t* desc, int batch,
+                               const int32_t* prefix_flat, const int32_t* new_slots, void* stream);
+
+/* bsgl_page_table_append: the decode step's B scalar writes (scheduler.py:486-488) in one launch:
+ * req_to_token[req_pool_indices[i], seq_lens[i] - 1] = slots[i]; seq_lens already counts the new
+ * token (scheduler.py:489-490). */
+int bsgl_page_table_append(int32_t* req_to_token, int64_t page_table_stride, int64_t n_rows,
+                           int row_len, const int64_t* req_pool_indices, const int64_t* seq_lens,
+                           const int32_t* slots, int batch, void* stream);
+
+/* The free-slot FIFO of BaseTokenToKVPool (memory_pool.py:46-102) as a ring in device memory.
+ * Head, tail and count live on the host (all sizes are known there), so neither call syncs:
+ *   pop : out[i] = ring[(head + i) mod capacity]            alloc, memory_pool.py:68-74
+ *   push: ring[(tail + i) mod capacity] = vals[i*val_stride] free,  memory_pool.py:76-80
+ * vals is int32 or int64 (vals_are_int64), e.g. a strided view of the page table. */
+int bsgl_slot_ring_pop(const int32_t* ring, int64_t capacity, int64_t head, int64_t n, int32_t* out,
+                       void* stream);
+int bsgl_slot_ring_push(int32_t* ring, int64_t capacity, int64_t tail, int64_t n, const void* vals,
+                        int64_t val_stride, int vals_are_int64, void* stream);
 
 #ifdef __cplusplus
 }

@@ -348,3 +348,51 @@ def greedy_sample(logits: torch.Tensor, extended_lens, prev_ids_per_request, pen
                 best, best_i = v, j
         out.append(best_i)
     return torch.tensor(out, dtype=torch.int64)
+
+
+# ------------------------------------------------------------------------------------------------------
+# K7: page-table writes and the free-slot FIFO (integer work, bit-exact)
+# ------------------------------------------------------------------------------------------------------
+def prefill_page_table_rows(req_to_token: torch.Tensor, rows, prefix_indices, new_slots, seq_lens) -> None:
+    """Reference scheduler.py:423-442 in place on `req_to_token` (int32 [R, C]): row rows[i] becomes
+    [prefix_indices[i] | the request's share of new_slots, in batch order | 0 ...] over ALL C cells
+    (the reference builds zeros([B, C]) and writes whole rows, so stale cells past seq_len are cleared)."""
+    C = int(req_to_token.shape[1])
+    off = 0
+    for i, row in enumerate(rows):
+        pre = [int(v) for v in prefix_indices[i]]
+        n_new = int(seq_lens[i]) - len(pre)
+        line = [0] * C
+        for c, v in enumerate(pre):
+            line[c] = v
+        for c in range(n_new):
+            line[len(pre) + c] = int(new_slots[off + c])
+        off += n_new
+        req_to_token[int(row)] = torch.tensor(line, dtype=torch.int32)
+
+
+def decode_page_table_append(req_to_token: torch.Tensor, rows, seq_lens_before, slots) -> None:
+    """Reference scheduler.py:485-489: the new token's slot goes to cell `seq_len` (the length BEFORE the
+    increment) of the request's row."""
+    for row, pos, slot in zip(rows, seq_lens_before, slots):
+        req_to_token[int(row), int(pos)] = int(slot)
+
+
+class SlotFifo:
+    """Reference BaseTokenToKVPool free list (memory_pool.py:46-84) as a plain list: slots 1..size, `alloc`
+    takes from the head (None when short), `free` appends at the tail in the given order, no sort, no de-dup."""
+
+    def __init__(self, size: int):
+        self.slots = list(range(1, size + 1))
+
+    def available_size(self) -> int:
+        return len(self.slots)
+
+    def alloc(self, n: int):
+        if n > len(self.slots):
+            return None
+        out, self.slots = self.slots[:n], self.slots[n:]
+        return out
+
+    def free(self, vals) -> None:
+        self.slots.extend(int(v) for v in vals)
