@@ -1,0 +1,410 @@
+// K8  o_proj GEMM with the tensor-parallel SUM all-reduce fused into its epilogue (sm_100a, NVLink peer memory).
+//
+// Replaces, under KV-head tensor parallelism: `o_proj(attn_output)`
+// (qwen2.py:166,195; bias-free, weight [hidden, Hq*D]) on this rank's column shard followed by
+// `tp_all_reduce_sum` (tp_runtime.py:28-33, dist.all_reduce over NCCL) -- two kernels, a 2 x [T, hidden]
+// HBM round trip and an NCCL launch per layer -- by ONE kernel per rank:
+//
+//   phase 1  partial[T, hidden] = attn_out[T, K_r] . W_r^T on tcgen05 tensor cores: TMA (2-D tensor maps,
+//            128B swizzle) feeds a 6-stage shared-memory ring, one thread issues tcgen05.mma M128 N128 K16
+//            into a double-buffered TMEM accumulator, and the epilogue warps push each finished 128x128
+//            tile as bf16 straight from registers into the OWNER rank's staging buffer over NVLink
+//            (peer-mapped memory, 512-byte coalesced bursts), then publish a per-(tile, source) flag with a
+//            system-scope release.  Tiles are visited owner-by-owner starting at rank+1, so every link is
+//            busy from the first tile on and a rank's own tiles come last.
+//   phase 2  the owner of a tile (tile % world) waits for its `world` partials, adds them in fp32 in rank
+//            order (the result is bit-identical everywhere because only the owner computes it), rounds once
+//            to bf16 and stores the final tile into EVERY rank's output buffer, then raises that tile's
+//            done-flag on every rank.
+//   phase 3  CTA 0 waits until every tile of the local output has been delivered.
+//
+// The transfer of tile i overlaps the MMAs of tile i+1 (TMEM double buffer) and the whole exchange overlaps
+// the GEMM tail; no NCCL call, no separate reduction pass over HBM.  Flags carry the call's epoch (monotonic),
+// staging and output buffers alternate with the epoch's parity: a rank can run at most one call ahead of its
+// peers (it cannot finish call n before every owner delivered call n), so two copies suffice.
+//
+// Bound: NVLink/NVSwitch bandwidth.  Bytes on the wire per rank = 2 (t-1)/t x T x hidden x 2 B.
+#include <cuda.h>
+
+#include "tcgen05.cuh"
+
+namespace bsgl {
+
+constexpr int kOpBM = 128, kOpBN = 128, kOpBK = 64;
+constexpr int kOpStages = 6;
+constexpr int kOpStageBytes = (kOpBM + kOpBN) * kOpBK * 2;   // 32 KB: A tile + B tile, bf16
+constexpr int kOpThreads = 192;                              // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int kOpTileBytes = kOpBM * kOpBN * 2;              // one bf16 partial tile in staging
+constexpr int kOpMaxWorld = 8;
+constexpr int kOpSmemBytes = kOpStages * kOpStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
+
+struct OprojComm {
+  uint8_t* staging[kOpMaxWorld];    // per rank: [2][world][max_slots] partial tiles (chunk-major 16-byte layout)
+  uint8_t* out[kOpMaxWorld];        // per rank: [2][max_tokens * hidden] bf16
+  uint32_t* flags[kOpMaxWorld];     // per rank: arrive[max_slots][8] then done[max_tiles]
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// Spin until *p >= want (epochs are monotonic).  A peer that never shows up traps this rank after ~4 s
+// instead of hanging the GPU.
+__device__ __forceinline__ void wait_flag_ge(const uint32_t* p, uint32_t want) {
+  if (ld_acquire_sys(p) >= want) return;
+  const uint64_t t0 = globaltimer_ns();
+  while (ld_acquire_sys(p) < want) {
+    __nanosleep(64);
+    if (globaltimer_ns() - t0 > 4000000000ull) __trap();
+  }
+}
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap* tmap, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          dst_smem),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
+}
+
+// Local visiting order: position i -> global tile id.  Owner groups (rank+1, rank+2, ..., rank) in turn;
+// owner o holds tiles o, o + world, o + 2 world, ...
+__device__ __forceinline__ int tile_at(int i, int n_tiles, int rank, int world) {
+  for (int g = 0; g < world; ++g) {
+    const int o = (rank + 1 + g) % world;
+    const int cnt = (n_tiles - o + world - 1) / world;
+    if (i < cnt) return o + world * i;
+    i -= cnt;
+  }
+  return -1;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kOpThreads, 1)
+oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                       const OprojComm comm, int M, int N, int K, int rank, int world, int max_slots,
+                       int64_t out_parity_bytes, uint32_t epoch) {
+  extern __shared__ uint8_t smem_dyn[];
+  const uint32_t raw = smem_u32(smem_dyn);
+  const uint32_t base = (raw + 1023u) & ~1023u;          // SWIZZLE_128B tiles need 1024-byte alignment
+  uint8_t* smem = smem_dyn + (base - raw);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_nt = N / kOpBN, n_mt = (M + kOpBM - 1) / kOpBM, n_tiles = n_mt * n_nt, n_kb = K / kOpBK;
+  const uint32_t par = epoch & 1u;
+
+  const uint32_t bar0 = base + kOpStages * kOpStageBytes;
+  const uint32_t full0 = bar0, empty0 = bar0 + 8 * kOpStages, accf0 = empty0 + 8 * kOpStages, acce0 = accf0 + 16;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kOpStages * kOpStageBytes + 8 * (2 * kOpStages + 4));
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kOpStages; ++s) {
+      mbar_init(full0 + 8 * s, 1);      // producer's arrive.expect_tx; TMA completes the bytes
+      mbar_init(empty0 + 8 * s, 1);     // tcgen05.commit
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(accf0 + 8 * b, 1);      // tcgen05.commit after a tile's last MMA
+      mbar_init(acce0 + 8 * b, 128);    // the epilogue threads, once the accumulator is in registers
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tc::tmem_alloc(smem_u32(tmem_slot), 256);
+    tc::tmem_relinquish();
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    // ======================================================== TMA producer
+    if (lane == 0) {
+      tma_prefetch_desc(&tm_a);
+      tma_prefetch_desc(&tm_b);
+      uint32_t it = 0;
+      for (int i = blockIdx.x; i < n_tiles; i += gridDim.x) {
+        const int tile = tile_at(i, n_tiles, rank, world);
+        const int m0 = (tile / n_nt) * kOpBM, n0 = (tile % n_nt) * kOpBN;
+        for (int kb = 0; kb < n_kb; ++kb, ++it) {
+          const uint32_t s = it % kOpStages, ph = (it / kOpStages) & 1u;
+          mbar_wait_guarded(empty0 + 8 * s, ph ^ 1u);
+          mbar_arrive_expect_tx(full0 + 8 * s, kOpStageBytes);
+          const uint32_t a_dst = base + s * kOpStageBytes;
+          tma_load_2d(a_dst, &tm_a, kb * kOpBK, m0, full0 + 8 * s);                      // rows past M arrive as zeros
+          tma_load_2d(a_dst + kOpBM * kOpBK * 2, &tm_b, kb * kOpBK, n0, full0 + 8 * s);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================================================== MMA issuer (warp-uniform loop, one elected lane)
+    constexpr uint32_t idesc = tc::instr_desc<T>(kOpBM, kOpBN, 0, 0);
+    uint32_t it = 0, tcount = 0;
+    for (int i = blockIdx.x; i < n_tiles; i += gridDim.x, ++tcount) {
+      const uint32_t buf = tcount & 1u;
+      mbar_wait_guarded(acce0 + 8 * buf, ((tcount >> 1) & 1u) ^ 1u);
+      tc::fence_after_sync();
+      for (int kb = 0; kb < n_kb; ++kb, ++it) {
+        const uint32_t s = it % kOpStages, ph = (it / kOpStages) & 1u;
+        mbar_wait_guarded(full0 + 8 * s, ph);
+        tc::fence_after_sync();
+        const uint32_t a = base + s * kOpStageBytes, b = a + kOpBM * kOpBK * 2;
+        if (tc::elect_one()) {
+#pragma unroll
+          for (int kk = 0; kk < kOpBK / 16; ++kk)
+            tc::mma_ss(tmem + buf * kOpBN, tc::smem_desc_sw128(a + kk * 32, 16, 1024),
+                       tc::smem_desc_sw128(b + kk * 32, 16, 1024), idesc, (kb | kk) != 0 ? 1u : 0u);
+          tc::commit(empty0 + 8 * s);
+          if (kb == n_kb - 1) tc::commit(accf0 + 8 * buf);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ======================================================== epilogue: push partial tiles, then reduce owned tiles
+    const int q = warp & 3;                                   // TMEM lane quadrant of this warp
+    const int row = q * 32 + lane;
+    const int etid = (warp - 2) * 32 + lane;                  // 0..127
+    const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+    uint32_t tcount = 0;
+    for (int i = blockIdx.x; i < n_tiles; i += gridDim.x, ++tcount) {
+      const int tile = tile_at(i, n_tiles, rank, world);
+      const int owner = tile % world, slot = tile / world;
+      const uint32_t buf = tcount & 1u;
+      mbar_wait_guarded(accf0 + 8 * buf, (tcount >> 1) & 1u);
+      tc::fence_after_sync();
+      uint32_t acc[4][32];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tc::ld32(tmem + lane_base + buf * kOpBN + c * 32, acc[c]);
+      tc::wait_ld();
+      tc::fence_before_sync();
+      mbar_arrive(acce0 + 8 * buf);                           // the MMA warp may start the tile after next
+      // staging layout: 16-byte chunk c of row r at (c * 128 + r) * 16 -> a warp store is one 512-byte burst
+      uint4* dst = reinterpret_cast<uint4*>(comm.staging[owner] +
+                                            ((int64_t)(par * world + rank) * max_slots + slot) * kOpTileBytes);
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        const uint32_t* v = &acc[c >> 2][(c & 3) * 8];
+        uint4 pk;
+        pk.x = pack2<T>(__uint_as_float(v[0]), __uint_as_float(v[1]));
+        pk.y = pack2<T>(__uint_as_float(v[2]), __uint_as_float(v[3]));
+        pk.z = pack2<T>(__uint_as_float(v[4]), __uint_as_float(v[5]));
+        pk.w = pack2<T>(__uint_as_float(v[6]), __uint_as_float(v[7]));
+        dst[c * 128 + row] = pk;
+      }
+      __threadfence_system();
+      named_bar_sync(1, 128);
+      if (etid == 0) st_release_sys(comm.flags[owner] + slot * kOpMaxWorld + rank, epoch);
+    }
+
+    // ---- phase 2: tiles this rank owns (tile = rank + world * j)
+    const int n_owned = (n_tiles - rank + world - 1) / world;
+    uint32_t* my_flags = comm.flags[rank];
+    const int done_off = max_slots * kOpMaxWorld;
+    for (int j = blockIdx.x; j < n_owned; j += gridDim.x) {
+      const int tile = rank + world * j;
+      const int m0 = (tile / n_nt) * kOpBM, n0 = (tile % n_nt) * kOpBN;
+      if (etid < world) wait_flag_ge(my_flags + j * kOpMaxWorld + etid, epoch);
+      named_bar_sync(1, 128);
+      const uint8_t* part0 = comm.staging[rank] + ((int64_t)par * world * max_slots + j) * kOpTileBytes;
+      const int64_t src_stride = (int64_t)max_slots * kOpTileBytes;
+#pragma unroll 2
+      for (int itx = 0; itx < 16; ++itx) {
+        const int item = itx * 128 + etid;
+        const int c = item & 15, r = item >> 4;              // 16 lanes cover one 256-byte output row segment
+        float sum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int s = 0; s < world; ++s) {                     // fixed order: the result does not depend on arrival order
+          const uint4 v = __ldcg(reinterpret_cast<const uint4*>(part0 + s * src_stride) + c * 128 + r);
+          const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float lo, hi;
+            if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+              lo = __uint_as_float(w4[e] << 16);
+              hi = __uint_as_float(w4[e] & 0xffff0000u);
+            } else {
+              const __half2 h = *reinterpret_cast<const __half2*>(&w4[e]);
+              lo = __low2float(h);
+              hi = __high2float(h);
+            }
+            sum[2 * e] += lo;
+            sum[2 * e + 1] += hi;
+          }
+        }
+        if (m0 + r < M) {
+          uint4 pk;
+          pk.x = pack2<T>(sum[0], sum[1]);
+          pk.y = pack2<T>(sum[2], sum[3]);
+          pk.z = pack2<T>(sum[4], sum[5]);
+          pk.w = pack2<T>(sum[6], sum[7]);
+          const int64_t off = (int64_t)par * out_parity_bytes + ((int64_t)(m0 + r) * N + n0 + c * 8) * 2;
+          for (int p = 0; p < world; ++p) *reinterpret_cast<uint4*>(comm.out[p] + off) = pk;
+        }
+      }
+      __threadfence_system();
+      named_bar_sync(1, 128);
+      if (etid < world) st_release_sys(comm.flags[etid] + done_off + tile, epoch);
+    }
+
+    // ---- phase 3: the local output is complete once every owner delivered every tile
+    if (blockIdx.x == 0) {
+      for (int tile = etid; tile < n_tiles; tile += 128) wait_flag_ge(my_flags + done_off + tile, epoch);
+    }
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc::fence_after_sync();
+    tc::tmem_dealloc(tmem, 256);
+  }
+}
+
+}  // namespace bsgl
+
+// ------------------------------------------------------------------------------------ host side
+namespace bsgl {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+// [rows, K] row-major 16-bit matrix, rows `ld` elements apart -> 2-D map with a {64 x 128} box, 128B swizzle.
+static int make_map(CUtensorMap* m, const void* ptr, int64_t rows, int64_t K, int64_t ld, int dtype) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  BSGL_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)kOpBK, (cuuint32_t)kOpBM};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, dtype == BSGL_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                  const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  BSGL_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return BSGL_OK;
+}
+
+template <typename T>
+static int launch_oproj(const CUtensorMap& ta, const CUtensorMap& tb, const OprojComm& comm, int M, int N, int K,
+                        int rank, int world, int max_slots, int64_t out_parity_bytes, uint32_t epoch,
+                        cudaStream_t stream) {
+  auto kern = oproj_allreduce_kernel<T>;
+  static thread_local int configured_dev = -1;
+  int dev = 0, sms = 0;
+  BSGL_CUDA_TRY(cudaGetDevice(&dev));
+  if (configured_dev != dev) {
+    BSGL_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kOpSmemBytes));
+    configured_dev = dev;
+  }
+  BSGL_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int n_tiles = ((M + kOpBM - 1) / kOpBM) * (N / kOpBN);
+  // every CTA must be resident: phase 2 waits on tiles other CTAs of this grid produce
+  const int grid = n_tiles < sms ? n_tiles : sms;
+  kern<<<grid, kOpThreads, kOpSmemBytes, stream>>>(ta, tb, comm, M, N, K, rank, world, max_slots, out_parity_bytes,
+                                                   epoch);
+  return check_launch("oproj_allreduce_kernel");
+}
+
+}  // namespace bsgl
+
+extern "C" int bsgl_comm_alloc(int64_t bytes, void** dev_ptr, void* ipc_handle_64) {
+  using namespace bsgl;
+  BSGL_REQUIRE(bytes > 0 && dev_ptr && ipc_handle_64, "bsgl_comm_alloc: bad arguments");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* p = nullptr;
+  BSGL_CUDA_TRY(cudaMalloc(&p, (size_t)bytes));
+  BSGL_CUDA_TRY(cudaMemset(p, 0, (size_t)bytes));
+  BSGL_CUDA_TRY(cudaDeviceSynchronize());
+  cudaIpcMemHandle_t h;
+  BSGL_CUDA_TRY(cudaIpcGetMemHandle(&h, p));
+  memcpy(ipc_handle_64, &h, 64);
+  *dev_ptr = p;
+  return BSGL_OK;
+}
+
+extern "C" int bsgl_comm_open(const void* ipc_handle_64, void** dev_ptr) {
+  using namespace bsgl;
+  BSGL_REQUIRE(ipc_handle_64 && dev_ptr, "bsgl_comm_open: null pointer");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, ipc_handle_64, 64);
+  BSGL_CUDA_TRY(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return BSGL_OK;
+}
+
+extern "C" int bsgl_comm_close(void* dev_ptr) {
+  using namespace bsgl;
+  if (dev_ptr) BSGL_CUDA_TRY(cudaIpcCloseMemHandle(dev_ptr));
+  return BSGL_OK;
+}
+
+extern "C" int bsgl_comm_free(void* dev_ptr) {
+  using namespace bsgl;
+  if (dev_ptr) BSGL_CUDA_TRY(cudaFree(dev_ptr));
+  return BSGL_OK;
+}
+
+extern "C" int bsgl_oproj_allreduce(const void* a, int64_t lda, const void* w, int64_t ldw, int n_tokens, int hidden,
+                                    int k_local, int rank, int world, void* const* staging_ptrs,
+                                    void* const* out_ptrs, void* const* flag_ptrs, int max_slots, int max_tiles,
+                                    int64_t out_parity_bytes, uint32_t epoch, int dtype, void* stream) {
+  using namespace bsgl;
+  BSGL_REQUIRE(n_tokens >= 0, "bsgl_oproj_allreduce: negative token count");
+  BSGL_REQUIRE(a && w && staging_ptrs && out_ptrs && flag_ptrs, "bsgl_oproj_allreduce: null pointer");
+  BSGL_REQUIRE(world >= 1 && world <= kOpMaxWorld && rank >= 0 && rank < world,
+               "bsgl_oproj_allreduce: rank %d / world %d out of range (max %d)", rank, world, kOpMaxWorld);
+  BSGL_REQUIRE(hidden > 0 && hidden % kOpBN == 0, "bsgl_oproj_allreduce: hidden %d is not a multiple of %d", hidden,
+               kOpBN);
+  BSGL_REQUIRE(k_local > 0 && k_local % kOpBK == 0, "bsgl_oproj_allreduce: K %d is not a multiple of %d", k_local,
+               kOpBK);
+  BSGL_REQUIRE(dtype == BSGL_BF16 || dtype == BSGL_F16, "bsgl_oproj_allreduce: dtype must be bf16 or fp16");
+  BSGL_REQUIRE(lda >= k_local && ldw >= k_local && lda % 8 == 0 && ldw % 8 == 0 && (uintptr_t)a % 16 == 0 &&
+                   (uintptr_t)w % 16 == 0,
+               "bsgl_oproj_allreduce: operands must be 16-byte aligned with row strides that are multiples of 8");
+  BSGL_REQUIRE(epoch > 0, "bsgl_oproj_allreduce: epoch starts at 1 (flags are zero-initialised)");
+  if (n_tokens == 0) return BSGL_OK;
+  const int n_tiles = ((n_tokens + kOpBM - 1) / kOpBM) * (hidden / kOpBN);
+  BSGL_REQUIRE(n_tiles <= max_tiles && (n_tiles + world - 1) / world <= max_slots,
+               "bsgl_oproj_allreduce: %d tiles exceed the communicator (max_tiles %d, max_slots %d)", n_tiles,
+               max_tiles, max_slots);
+  BSGL_REQUIRE((int64_t)n_tokens * hidden * 2 <= out_parity_bytes, "bsgl_oproj_allreduce: output buffer too small");
+  OprojComm comm;
+  for (int i = 0; i < kOpMaxWorld; ++i) {
+    const int j = i < world ? i : 0;
+    BSGL_REQUIRE(staging_ptrs[j] && out_ptrs[j] && flag_ptrs[j], "bsgl_oproj_allreduce: null peer pointer");
+    comm.staging[i] = (uint8_t*)staging_ptrs[j];
+    comm.out[i] = (uint8_t*)out_ptrs[j];
+    comm.flags[i] = (uint32_t*)flag_ptrs[j];
+  }
+  CUtensorMap ta, tb;
+  int rc = make_map(&ta, a, n_tokens, k_local, lda, dtype);
+  if (rc != BSGL_OK) return rc;
+  rc = make_map(&tb, w, hidden, k_local, ldw, dtype);
+  if (rc != BSGL_OK) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (dtype == BSGL_BF16)
+    return launch_oproj<__nv_bfloat16>(ta, tb, comm, n_tokens, hidden, k_local, rank, world, max_slots,
+                                       out_parity_bytes, epoch, s);
+  return launch_oproj<__half>(ta, tb, comm, n_tokens, hidden, k_local, rank, world, max_slots, out_parity_bytes, epoch,
+                              s);
+}

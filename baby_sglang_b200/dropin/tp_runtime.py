@@ -31,7 +31,7 @@ import torch
 import torch.distributed as dist
 
 __all__ = ["init_tp", "tp_all_reduce_sum", "tp_all_gather", "tp_broadcast", "plan_parallelism", "ParallelPlan",
-           "shard_attention_heads", "kv_pool_config", "dp_partition", "dp_gather_outputs"]
+           "shard_attention_heads", "kv_pool_config", "dp_partition", "dp_gather_outputs", "FusedOProjAllReduce"]
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -120,7 +120,82 @@ def _attention_modules(model: torch.nn.Module):
             yield m
 
 
-def shard_attention_heads(model: torch.nn.Module, rank: int, world_size: int, tp_group) -> ParallelPlan:
+class FusedOProjAllReduce:
+    """`o_proj` + SUM all-reduce as ONE kernel per rank over NVLink peer memory (K8, `bsgl_oproj_allreduce`),
+    in place of `F.linear` + `dist.all_reduce` (qwen2.py:195 + tp_runtime.py:28-33).
+
+    One communicator serves every layer: a staging area for partial tiles, two output buffers and the
+    flags, allocated once through the C ABI (cudaMalloc + CUDA IPC), exported to the peers with
+    `dist.all_gather_object` and mapped here.  Calls are numbered (`epoch`); every rank must make the same
+    sequence of calls, which the replicated scheduler guarantees.  The returned tensor is a view of this rank's
+    output buffer of the call's parity: it stays valid until the call after next (the reference's layer consumes
+    it at once: residual add + RMSNorm create new tensors, qwen2.py:113-121)."""
+
+    TILE = 128
+
+    def __init__(self, rank: int, world_size: int, tp_group, hidden: int, max_tokens: int,
+                 dtype: torch.dtype = torch.bfloat16, device=None):
+        from baby_sglang_b200 import ops
+        if hidden % self.TILE:
+            raise ValueError(f"hidden {hidden} is not a multiple of {self.TILE}")
+        if not 1 <= world_size <= 8:
+            raise ValueError("fused o_proj all-reduce supports 1..8 ranks")
+        self._ops, self.rank, self.world, self.group = ops, rank, world_size, tp_group
+        self.hidden, self.max_tokens, self.dtype = hidden, max_tokens, dtype
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.max_tiles = -(-max_tokens // self.TILE) * (hidden // self.TILE)
+        self.max_slots = -(-self.max_tiles // world_size)
+        up = lambda n: -(-n // 1024) * 1024
+        self.out_parity_bytes = up(max_tokens * hidden * 2)
+        staging_bytes = 2 * world_size * self.max_slots * self.TILE * self.TILE * 2
+        self._off_out = up(staging_bytes)
+        self._off_flags = self._off_out + 2 * self.out_parity_bytes
+        self.nbytes = self._off_flags + up((self.max_slots * 8 + self.max_tiles) * 4)
+        self._mine = ops.CommBuffer.alloc(self.nbytes)
+        self._peers = [None] * world_size
+        if world_size > 1:
+            handles = [None] * world_size
+            dist.all_gather_object(handles, self._mine.handle, group=tp_group)
+            for r, h in enumerate(handles):
+                self._peers[r] = self._mine if r == rank else ops.CommBuffer.open(h, self.nbytes)
+            dist.barrier(group=tp_group)
+        else:
+            self._peers[0] = self._mine
+        base = [b.ptr for b in self._peers]
+        self._staging = base
+        self._out = [p + self._off_out for p in base]
+        self._flags = [p + self._off_flags for p in base]
+        self.epoch = 0
+
+    def __call__(self, attn_out: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+        """attn_out [T, K_r] (this rank's heads), weight [hidden, K_r] (this rank's o_proj columns) ->
+        the all-reduced [T, hidden], bit-identical on every rank."""
+        T = int(attn_out.shape[0])
+        if T > self.max_tokens:
+            raise ValueError(f"{T} tokens exceed the communicator's max_tokens {self.max_tokens}")
+        if attn_out.dtype != self.dtype or weight.dtype != self.dtype or int(weight.shape[0]) != self.hidden:
+            raise ValueError("dtype / hidden size differ from the communicator's")
+        self.epoch += 1
+        self._ops.oproj_allreduce(attn_out, weight, self.rank, self.world, self._staging, self._out, self._flags,
+                                  self.max_slots, self.max_tiles, self.out_parity_bytes, self.epoch)
+        off = self._off_out + (self.epoch & 1) * self.out_parity_bytes
+        if T == 0:
+            return torch.empty(0, self.hidden, dtype=self.dtype, device=self.device)
+        return self._mine.as_tensor(off, (T, self.hidden), self.dtype, self.device)
+
+    def close(self) -> None:
+        if self.world > 1 and dist.is_initialized():
+            torch.cuda.synchronize()
+            dist.barrier(group=self.group)
+        for r, b in enumerate(self._peers):
+            if b is not None and r != self.rank:
+                b.release()
+        self._mine.release()
+        self._peers = []
+
+
+def shard_attention_heads(model: torch.nn.Module, rank: int, world_size: int, tp_group,
+                          fused_allreduce: "FusedOProjAllReduce" = None) -> ParallelPlan:
     """Mutate `model` in place so this rank computes its KV heads only.
 
     Per attention module: keep rows [q heads of this rank | k heads | v heads] of the fused QKV weight and
@@ -160,8 +235,24 @@ def shard_attention_heads(model: torch.nn.Module, rank: int, world_size: int, tp
                 holder.q_size, holder.kv_size = m.q_size, m.kv_size
                 holder.total_size = m.q_size + 2 * m.kv_size
         m.attn.tp_q_head_num, m.attn.tp_k_head_num, m.attn.tp_v_head_num = m.num_heads, m.num_kv_heads, m.num_kv_heads
-        m.o_proj.register_forward_hook(lambda _mod, _inp, out, g=tp_group: tp_all_reduce_sum(out, g))
+        if fused_allreduce is None:
+            m.o_proj.register_forward_hook(lambda _mod, _inp, out, g=tp_group: tp_all_reduce_sum(out, g))
+        else:
+            m.o_proj.forward = _fused_oproj_forward(m.o_proj, fused_allreduce, tp_group)
     return plan
+
+
+def _fused_oproj_forward(o_proj: torch.nn.Linear, comm: "FusedOProjAllReduce", tp_group):
+    """`o_proj.forward` replacement: K8 for batches the communicator was sized for, the NCCL pair otherwise."""
+    def forward(x: torch.Tensor) -> torch.Tensor:
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, x.shape[-1])
+        if x2.shape[0] > comm.max_tokens:
+            return tp_all_reduce_sum(torch.nn.functional.linear(x, o_proj.weight), tp_group)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        return comm(x2, o_proj.weight).view(*lead, comm.hidden)
+    return forward
 
 
 def kv_pool_config(config, plan: ParallelPlan):

@@ -518,3 +518,61 @@ def slot_ring_push(ring: torch.Tensor, tail: int, vals: torch.Tensor) -> None:
                                          int(vals.stride(0)), 1 if vals.dtype == torch.int64 else 0, _stream())
     _lib.check(rc, "bsgl_slot_ring_push")
     _count()
+
+
+# --------------------------------------------------------------------------------------- K8
+class CommBuffer:
+    """A device buffer other processes on the node can map (cudaMalloc + CUDA IPC through the C ABI).
+    `ptr` is the local address, `handle` the 64 bytes a peer passes to `CommBuffer.open`."""
+
+    def __init__(self, ptr: int, nbytes: int, handle: Optional[bytes], owned: bool):
+        self.ptr, self.nbytes, self.handle, self._owned = ptr, nbytes, handle, owned
+
+    @classmethod
+    def alloc(cls, nbytes: int) -> "CommBuffer":
+        if not torch.cuda.is_available():
+            raise _lib.BsglError("communicator buffers need a CUDA device; there is no CPU path")
+        p = ctypes.c_void_p(0)
+        h = ctypes.create_string_buffer(64)
+        _lib.check(_lib.load().bsgl_comm_alloc(int(nbytes), ctypes.byref(p), h), "bsgl_comm_alloc")
+        return cls(int(p.value), int(nbytes), bytes(h.raw), True)
+
+    @classmethod
+    def open(cls, handle: bytes, nbytes: int) -> "CommBuffer":
+        p = ctypes.c_void_p(0)
+        _lib.check(_lib.load().bsgl_comm_open(ctypes.c_char_p(handle), ctypes.byref(p)), "bsgl_comm_open")
+        return cls(int(p.value), int(nbytes), None, False)
+
+    def release(self) -> None:
+        if self.ptr:
+            lib = _lib.load()
+            _lib.check(lib.bsgl_comm_free(self.ptr) if self._owned else lib.bsgl_comm_close(self.ptr), "bsgl_comm_free")
+            self.ptr = 0
+
+    def as_tensor(self, offset_bytes: int, shape, dtype: torch.dtype, device) -> torch.Tensor:
+        """Zero-copy torch view of a region of the buffer (via __cuda_array_interface__)."""
+        typestr = {torch.bfloat16: "<u2", torch.float16: "<f2", torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
+        holder = type("_CAI", (), {})()
+        holder.__cuda_array_interface__ = {"shape": tuple(int(x) for x in shape), "typestr": typestr,
+                                           "data": (self.ptr + int(offset_bytes), False), "version": 3}
+        t = torch.as_tensor(holder, device=device)
+        return t.view(dtype) if t.dtype != dtype else t
+
+
+def oproj_allreduce(a: torch.Tensor, w: torch.Tensor, rank: int, world: int, staging_ptrs, out_ptrs, flag_ptrs,
+                    max_slots: int, max_tiles: int, out_parity_bytes: int, epoch: int) -> None:
+    """K8 launch: this rank's o_proj partial GEMM with the SUM all-reduce fused in (reference qwen2.py:195 +
+    tp_runtime.py:28-33).  `a` [T, K_r] and `w` [hidden, K_r] are this rank's shard; the result lands in every
+    rank's output buffer at parity `epoch & 1`.  All ranks must call with the same epoch."""
+    _require_cuda(a, w)
+    if a.dtype != w.dtype or a.dim() != 2 or w.dim() != 2 or a.shape[1] != w.shape[1]:
+        raise _lib.BsglError(f"oproj_allreduce: a {tuple(a.shape)} {a.dtype} vs w {tuple(w.shape)} {w.dtype}")
+    if a.stride(1) != 1 or w.stride(1) != 1:
+        raise _lib.BsglError("oproj_allreduce: operands need unit inner stride")
+    arr = ctypes.c_void_p * world
+    rc = _lib.load().bsgl_oproj_allreduce(
+        a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), int(a.shape[0]), int(w.shape[0]), int(a.shape[1]),
+        int(rank), int(world), arr(*staging_ptrs), arr(*out_ptrs), arr(*flag_ptrs), int(max_slots), int(max_tiles),
+        int(out_parity_bytes), int(epoch), dtype_code(a.dtype), _stream())
+    _lib.check(rc, "bsgl_oproj_allreduce")
+    _count()

@@ -26,6 +26,7 @@
  *   bsgl_page_table_write_rows  prefill page-table rows                    scheduler.py:423-442
  *   bsgl_page_table_append      decode page-table cells                    scheduler.py:486-488
  *   bsgl_slot_ring_pop / _push  BaseTokenToKVPool.alloc / free             memory_pool.py:68-80
+ *   bsgl_oproj_allreduce        o_proj + tp_all_reduce_sum (KV-head TP)    qwen2.py:166,195, tp_runtime.py:28-33
  *
  * Layout conventions (identical to the reference's tensors):
  *   q        [rows, n_q_heads, head_dim]            contiguous, bf16 or fp16
@@ -211,6 +212,34 @@ int bsgl_slot_ring_pop(const int32_t* ring, int64_t capacity, int64_t head, int6
                        void* stream);
 int bsgl_slot_ring_push(int32_t* ring, int64_t capacity, int64_t tail, int64_t n, const void* vals,
                         int64_t val_stride, int vals_are_int64, void* stream);
+
+/* K8: o_proj GEMM with the KV-head-TP SUM all-reduce fused into its epilogue over
+ * NVLink peer memory.  Replaces `o_proj(attn_output)` (qwen2.py:166,195) + `tp_all_reduce_sum`
+ * (tp_runtime.py:28-33) with one kernel per rank.
+ *
+ * Communicator memory is the one thing this library allocates itself: it has to be exportable to the peer
+ * processes (cudaMalloc + CUDA IPC), which torch's caching allocator does not promise.
+ *   bsgl_comm_alloc  cudaMalloc + zero-fill + IPC export; handle is 64 bytes to hand to the peers
+ *   bsgl_comm_open   map a peer's buffer into this process (peer access enabled lazily)
+ *   bsgl_comm_close / bsgl_comm_free   the inverse of open / alloc
+ *
+ * bsgl_oproj_allreduce: out[T, hidden] = SUM_ranks( a_r[T, K_r] . w_r[hidden, K_r]^T ), identical bits on every rank.
+ *   a            [n_tokens, k_local]  this rank's attention output, rows lda elements apart (bf16/fp16)
+ *   w            [hidden, k_local]    this rank's column shard of o_proj.weight, rows ldw elements apart
+ *   staging_ptrs [world]  every rank's staging buffer as mapped here: 2 * world * max_slots * 32 KiB
+ *   out_ptrs     [world]  every rank's output buffer: 2 * out_parity_bytes; this rank reads its own at
+ *                         out_ptrs[rank] + (epoch & 1) * out_parity_bytes after the call (stream-ordered)
+ *   flag_ptrs    [world]  every rank's flags: (max_slots * 8 + max_tiles) uint32, zero-initialised
+ *   epoch        1, 2, 3, ... the same on every rank for the same call; all ranks must make the same calls
+ * hidden % 128 == 0, k_local % 64 == 0, world <= 8.  A peer that never arrives traps the kernel after ~4 s. */
+int bsgl_comm_alloc(int64_t bytes, void** dev_ptr, void* ipc_handle_64);
+int bsgl_comm_open(const void* ipc_handle_64, void** dev_ptr);
+int bsgl_comm_close(void* dev_ptr);
+int bsgl_comm_free(void* dev_ptr);
+int bsgl_oproj_allreduce(const void* a, int64_t lda, const void* w, int64_t ldw, int n_tokens, int hidden,
+                         int k_local, int rank, int world, void* const* staging_ptrs,
+                         void* const* out_ptrs, void* const* flag_ptrs, int max_slots, int max_tiles,
+                         int64_t out_parity_bytes, uint32_t epoch, int dtype, void* stream);
 
 #ifdef __cplusplus
 }

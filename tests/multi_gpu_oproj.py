@@ -1,0 +1,97 @@
+"""K8 under torchrun (one process per GPU, NCCL for the plumbing only): fused o_proj + all-reduce vs the pair it
+replaces (`F.linear` on the rank's shard + `dist.all_reduce`, qwen2.py:195 + tp_runtime.py:28-33).
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
+        tests/multi_gpu_oproj.py [--bench]
+
+Checks per case: (1) the result is bit-identical on every rank; (2) it is within bf16 rounding of the fp32 sum of
+the ranks' exact partial products (the NCCL pair rounds every partial to bf16 too, and then adds in bf16);
+(3) it is within tolerance of the NCCL pair.  Prints one JSON line per case on rank 0 and exits non-zero on failure.
+"""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, REPO)
+from baby_sglang_b200 import DROPIN_DIR  # noqa: E402
+
+sys.path.insert(0, DROPIN_DIR)
+import tp_runtime  # noqa: E402
+
+
+def main():
+    bench = "--bench" in sys.argv
+    rank, world, group = tp_runtime.init_tp()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    # (tokens, hidden, full K = Hq * D): 32B decode C5, a ragged token count, 7B geometry, a tiny batch
+    cases = [(1024, 5120, 5120), (333, 5120, 5120), (256, 3584, 3584), (7, 1536, 1536)]
+    comm = tp_runtime.FusedOProjAllReduce(rank, world, group, hidden=5120, max_tokens=1024)
+    ok = True
+    for T, hidden, Kfull in cases:
+        if Kfull % (world * 128) or hidden > comm.hidden:
+            continue
+        if hidden != comm.hidden:
+            comm.close()
+            comm = tp_runtime.FusedOProjAllReduce(rank, world, group, hidden=hidden, max_tokens=1024)
+        K = Kfull // world
+        g = torch.Generator(device="cpu").manual_seed(1000 * T + rank)
+        a = torch.randn(T, K, generator=g).to(dev, torch.bfloat16)
+        w = (torch.randn(hidden, K, generator=g) * 0.05).to(dev, torch.bfloat16)
+        for rep in range(3):                      # consecutive calls exercise both parities and epoch hand-over
+            out = comm(a, w).clone()
+        # the pair it replaces
+        ref = torch.nn.functional.linear(a, w)
+        dist.all_reduce(ref, group=group)
+        # fp32 truth: sum over ranks of the exact partials
+        exact = a.float() @ w.float().t()
+        dist.all_reduce(exact, group=group)
+        gathered = [torch.empty_like(out) for _ in range(world)]
+        dist.all_gather(gathered, out, group=group)
+        same = all(torch.equal(gathered[0], t) for t in gathered)
+        err_exact = (out.float() - exact).abs().max().item()
+        err_nccl = (out.float() - ref.float()).abs().max().item()
+        scale = exact.abs().max().item()
+        tol = 2.0 ** -7 * scale * (1 + world / 4)        # each partial is rounded to bf16 once, the sum once more
+        good = same and err_exact <= tol and err_nccl <= 2 * tol
+        ok &= good
+        line = {"case": f"T={T} hidden={hidden} K/rank={K}", "world": world, "bit_identical_across_ranks": same,
+                "max_abs_err_vs_fp32": err_exact, "max_abs_err_vs_nccl_pair": err_nccl, "tol": tol, "ok": good}
+        if bench and T == 1024:
+            def timed(fn, n=50):
+                for _ in range(5):
+                    fn()
+                torch.cuda.synchronize()
+                dist.barrier(group=group)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(n):
+                    fn()
+                e1.record()
+                torch.cuda.synchronize()
+                t = torch.tensor([e0.elapsed_time(e1) / n], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+                return float(t)
+
+            def pair():
+                o = torch.nn.functional.linear(a, w)
+                dist.all_reduce(o, group=group)
+                return o
+
+            line["fused_us"] = round(timed(lambda: comm(a, w)) * 1e3, 1)
+            line["nccl_pair_us"] = round(timed(pair) * 1e3, 1)
+            line["gemm_only_us"] = round(timed(lambda: torch.nn.functional.linear(a, w)) * 1e3, 1)
+            line["allreduce_bytes"] = T * hidden * 2
+        if rank == 0:
+            print(json.dumps(line), flush=True)
+    comm.close()
+    dist.barrier(group=group)
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
