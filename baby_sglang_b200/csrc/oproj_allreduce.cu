@@ -91,6 +91,66 @@ __device__ __forceinline__ int tile_at(int i, int n_tiles, int rank, int world) 
   return -1;
 }
 
+
+// Phase-2 worker: sum the `world` partial copies of one owned 128x128 tile (fp32, rank order), round once and
+// store the result into every rank's output.  IPB items (16-byte chunks) per thread are loaded for all sources
+// before the first add, so 16 loads per thread are in flight whatever the world size (W bounds `world`).
+template <typename T, int W>
+__device__ __forceinline__ void reduce_owned_tile(const OprojComm& comm, const uint8_t* part0, int64_t src_stride,
+                                                  int world, int etid, int m0, int n0, int M, int N,
+                                                  int64_t out_base) {
+  constexpr int IPB = 16 / W;
+#pragma unroll 1
+  for (int it0 = 0; it0 < 16; it0 += IPB) {
+    uint4 v[IPB][W];
+#pragma unroll
+    for (int u = 0; u < IPB; ++u) {
+      const int item = (it0 + u) * 128 + etid;
+      const int c = item & 15, r = item >> 4;                // 16 lanes cover one 256-byte output row segment
+#pragma unroll
+      for (int s = 0; s < W; ++s)
+        if (s < world) v[u][s] = __ldcg(reinterpret_cast<const uint4*>(part0 + s * src_stride) + c * 128 + r);
+    }
+#pragma unroll
+    for (int u = 0; u < IPB; ++u) {
+      const int item = (it0 + u) * 128 + etid;
+      const int c = item & 15, r = item >> 4;
+      float sum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int s = 0; s < W; ++s) {                          // fixed order: independent of arrival order
+        if (s < world) {
+          const uint32_t w4[4] = {v[u][s].x, v[u][s].y, v[u][s].z, v[u][s].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float lo, hi;
+            if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+              lo = __uint_as_float(w4[e] << 16);
+              hi = __uint_as_float(w4[e] & 0xffff0000u);
+            } else {
+              const __half2 h = *reinterpret_cast<const __half2*>(&w4[e]);
+              lo = __low2float(h);
+              hi = __high2float(h);
+            }
+            sum[2 * e] += lo;
+            sum[2 * e + 1] += hi;
+          }
+        }
+      }
+      if (m0 + r < M) {
+        uint4 pk;
+        pk.x = pack2<T>(sum[0], sum[1]);
+        pk.y = pack2<T>(sum[2], sum[3]);
+        pk.z = pack2<T>(sum[4], sum[5]);
+        pk.w = pack2<T>(sum[6], sum[7]);
+        const int64_t off = out_base + ((int64_t)(m0 + r) * N + n0 + c * 8) * 2;
+#pragma unroll
+        for (int p = 0; p < W; ++p)
+          if (p < world) *reinterpret_cast<uint4*>(comm.out[p] + off) = pk;
+      }
+    }
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kOpThreads, 1)
 oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
@@ -202,8 +262,7 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
         pk.w = pack2<T>(__uint_as_float(v[6]), __uint_as_float(v[7]));
         dst[c * 128 + row] = pk;
       }
-      __threadfence_system();
-      named_bar_sync(1, 128);
+      named_bar_sync(1, 128);      // bar.sync orders the 128 threads' stores before thread 0's release (cumulative)
       if (etid == 0) st_release_sys(comm.flags[owner] + slot * kOpMaxWorld + rank, epoch);
     }
 
@@ -218,41 +277,14 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
       named_bar_sync(1, 128);
       const uint8_t* part0 = comm.staging[rank] + ((int64_t)par * world * max_slots + j) * kOpTileBytes;
       const int64_t src_stride = (int64_t)max_slots * kOpTileBytes;
-#pragma unroll 2
-      for (int itx = 0; itx < 16; ++itx) {
-        const int item = itx * 128 + etid;
-        const int c = item & 15, r = item >> 4;              // 16 lanes cover one 256-byte output row segment
-        float sum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        for (int s = 0; s < world; ++s) {                     // fixed order: the result does not depend on arrival order
-          const uint4 v = __ldcg(reinterpret_cast<const uint4*>(part0 + s * src_stride) + c * 128 + r);
-          const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            float lo, hi;
-            if constexpr (std::is_same<T, __nv_bfloat16>::value) {
-              lo = __uint_as_float(w4[e] << 16);
-              hi = __uint_as_float(w4[e] & 0xffff0000u);
-            } else {
-              const __half2 h = *reinterpret_cast<const __half2*>(&w4[e]);
-              lo = __low2float(h);
-              hi = __high2float(h);
-            }
-            sum[2 * e] += lo;
-            sum[2 * e + 1] += hi;
-          }
-        }
-        if (m0 + r < M) {
-          uint4 pk;
-          pk.x = pack2<T>(sum[0], sum[1]);
-          pk.y = pack2<T>(sum[2], sum[3]);
-          pk.z = pack2<T>(sum[4], sum[5]);
-          pk.w = pack2<T>(sum[6], sum[7]);
-          const int64_t off = (int64_t)par * out_parity_bytes + ((int64_t)(m0 + r) * N + n0 + c * 8) * 2;
-          for (int p = 0; p < world; ++p) *reinterpret_cast<uint4*>(comm.out[p] + off) = pk;
-        }
-      }
-      __threadfence_system();
-      named_bar_sync(1, 128);
+      const int64_t out_base = (int64_t)par * out_parity_bytes;
+      if (world <= 2)
+        reduce_owned_tile<T, 2>(comm, part0, src_stride, world, etid, m0, n0, M, N, out_base);
+      else if (world <= 4)
+        reduce_owned_tile<T, 4>(comm, part0, src_stride, world, etid, m0, n0, M, N, out_base);
+      else
+        reduce_owned_tile<T, 8>(comm, part0, src_stride, world, etid, m0, n0, M, N, out_base);
+      named_bar_sync(1, 128);      // CTA-scope order of everyone's stores before the cumulative sys-scope release
       if (etid < world) st_release_sys(comm.flags[etid] + done_off + tile, epoch);
     }
 

@@ -165,6 +165,10 @@ class FusedOProjAllReduce:
         self._staging = base
         self._out = [p + self._off_out for p in base]
         self._flags = [p + self._off_flags for p in base]
+        # built once: the pointer tables the C ABI takes and the two output views (as_tensor costs tens of µs)
+        self._ptr_tables = ops.oproj_pointer_tables(self._staging, self._out, self._flags)
+        self._out_views = [self._mine.as_tensor(self._off_out + par * self.out_parity_bytes,
+                                                (max_tokens, hidden), dtype, self.device) for par in (0, 1)]
         self.epoch = 0
 
     def __call__(self, attn_out: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
@@ -176,12 +180,9 @@ class FusedOProjAllReduce:
         if attn_out.dtype != self.dtype or weight.dtype != self.dtype or int(weight.shape[0]) != self.hidden:
             raise ValueError("dtype / hidden size differ from the communicator's")
         self.epoch += 1
-        self._ops.oproj_allreduce(attn_out, weight, self.rank, self.world, self._staging, self._out, self._flags,
+        self._ops.oproj_allreduce(attn_out, weight, self.rank, self.world, *self._ptr_tables,
                                   self.max_slots, self.max_tiles, self.out_parity_bytes, self.epoch)
-        off = self._off_out + (self.epoch & 1) * self.out_parity_bytes
-        if T == 0:
-            return torch.empty(0, self.hidden, dtype=self.dtype, device=self.device)
-        return self._mine.as_tensor(off, (T, self.hidden), self.dtype, self.device)
+        return self._out_views[self.epoch & 1][:T]
 
     def close(self) -> None:
         if self.world > 1 and dist.is_initialized():

@@ -559,6 +559,12 @@ class CommBuffer:
         return t.view(dtype) if t.dtype != dtype else t
 
 
+def oproj_pointer_tables(staging_ptrs, out_ptrs, flag_ptrs):
+    """The three per-rank pointer tables of a communicator as ctypes arrays (build once, pass to every call)."""
+    arr = ctypes.c_void_p * len(staging_ptrs)
+    return arr(*staging_ptrs), arr(*out_ptrs), arr(*flag_ptrs)
+
+
 def oproj_allreduce(a: torch.Tensor, w: torch.Tensor, rank: int, world: int, staging_ptrs, out_ptrs, flag_ptrs,
                     max_slots: int, max_tiles: int, out_parity_bytes: int, epoch: int) -> None:
     """K8 launch: this rank's o_proj partial GEMM with the SUM all-reduce fused in (reference qwen2.py:195 +
@@ -569,10 +575,11 @@ def oproj_allreduce(a: torch.Tensor, w: torch.Tensor, rank: int, world: int, sta
         raise _lib.BsglError(f"oproj_allreduce: a {tuple(a.shape)} {a.dtype} vs w {tuple(w.shape)} {w.dtype}")
     if a.stride(1) != 1 or w.stride(1) != 1:
         raise _lib.BsglError("oproj_allreduce: operands need unit inner stride")
-    arr = ctypes.c_void_p * world
+    if not isinstance(staging_ptrs, ctypes.Array):
+        staging_ptrs, out_ptrs, flag_ptrs = oproj_pointer_tables(staging_ptrs, out_ptrs, flag_ptrs)
     rc = _lib.load().bsgl_oproj_allreduce(
         a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), int(a.shape[0]), int(w.shape[0]), int(a.shape[1]),
-        int(rank), int(world), arr(*staging_ptrs), arr(*out_ptrs), arr(*flag_ptrs), int(max_slots), int(max_tiles),
+        int(rank), int(world), staging_ptrs, out_ptrs, flag_ptrs, int(max_slots), int(max_tiles),
         int(out_parity_bytes), int(epoch), dtype_code(a.dtype), _stream())
     _lib.check(rc, "bsgl_oproj_allreduce")
     _count()
