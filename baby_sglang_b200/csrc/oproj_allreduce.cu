@@ -33,7 +33,7 @@ namespace bsgl {
 constexpr int kOpBM = 128, kOpBN = 128, kOpBK = 64;
 constexpr int kOpStages = 6;
 constexpr int kOpStageBytes = (kOpBM + kOpBN) * kOpBK * 2;   // 32 KB: A tile + B tile, bf16
-constexpr int kOpThreads = 192;                              // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int kOpThreads = 320;                              // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue, 6-9 owner reduce
 constexpr int kOpTileBytes = kOpBM * kOpBN * 2;              // one bf16 partial tile in staging
 constexpr int kOpMaxWorld = 8;
 constexpr int kOpSmemBytes = kOpStages * kOpStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
@@ -230,8 +230,8 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
         __syncwarp();
       }
     }
-  } else {
-    // ======================================================== epilogue: push partial tiles, then reduce owned tiles
+  } else if (warp < 6) {
+    // ======================================================== epilogue: push partial tiles to their owners
     const int q = warp & 3;                                   // TMEM lane quadrant of this warp
     const int row = q * 32 + lane;
     const int etid = (warp - 2) * 32 + lane;                  // 0..127
@@ -266,7 +266,17 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
       if (etid == 0) st_release_sys(comm.flags[owner] + slot * kOpMaxWorld + rank, epoch);
     }
 
-    // ---- phase 2: tiles this rank owns (tile = rank + world * j)
+    // ---- phase 3: the local output is complete once every owner delivered every tile
+    if (blockIdx.x == 0) {
+      const uint32_t* my_flags = comm.flags[rank];
+      const int done_off = max_slots * kOpMaxWorld;
+      for (int tile = etid; tile < n_tiles; tile += 128) wait_flag_ge(my_flags + done_off + tile, epoch);
+    }
+  } else {
+    // ======================================================== owner reduce (phase 2), concurrent with phase 1:
+    // owned tiles complete in increasing j (every rank visits an owner's tiles in the same order, its own last),
+    // so these warps trail the GEMM by about one tile instead of starting after it
+    const int etid = (warp - 6) * 32 + lane;                  // 0..127
     const int n_owned = (n_tiles - rank + world - 1) / world;
     uint32_t* my_flags = comm.flags[rank];
     const int done_off = max_slots * kOpMaxWorld;
@@ -274,7 +284,7 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
       const int tile = rank + world * j;
       const int m0 = (tile / n_nt) * kOpBM, n0 = (tile % n_nt) * kOpBN;
       if (etid < world) wait_flag_ge(my_flags + j * kOpMaxWorld + etid, epoch);
-      named_bar_sync(1, 128);
+      named_bar_sync(2, 128);
       const uint8_t* part0 = comm.staging[rank] + ((int64_t)par * world * max_slots + j) * kOpTileBytes;
       const int64_t src_stride = (int64_t)max_slots * kOpTileBytes;
       const int64_t out_base = (int64_t)par * out_parity_bytes;
@@ -284,14 +294,10 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
         reduce_owned_tile<T, 4>(comm, part0, src_stride, world, etid, m0, n0, M, N, out_base);
       else
         reduce_owned_tile<T, 8>(comm, part0, src_stride, world, etid, m0, n0, M, N, out_base);
-      named_bar_sync(1, 128);      // CTA-scope order of everyone's stores before the cumulative sys-scope release
+      named_bar_sync(2, 128);      // CTA-scope order of everyone's stores before the cumulative sys-scope release
       if (etid < world) st_release_sys(comm.flags[etid] + done_off + tile, epoch);
     }
 
-    // ---- phase 3: the local output is complete once every owner delivered every tile
-    if (blockIdx.x == 0) {
-      for (int tile = etid; tile < n_tiles; tile += 128) wait_flag_ge(my_flags + done_off + tile, epoch);
-    }
   }
 
   __syncthreads();
