@@ -92,6 +92,8 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
   const int cta = blockIdx.x;
   if (cta >= n_eff || n_tiles == 0) return;
 
+  // the merge kernel behind us is a programmatic dependent: let it launch and park at its griddepcontrol.wait
+  asm volatile("griddepcontrol.launch_dependents;");
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* stages = smem;
   float* scratch = reinterpret_cast<float*>(smem + NST * C::STAGE_BYTES);

@@ -318,7 +318,8 @@ def paged_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor,
     _count()
     if merge:
         rc = lib.bsgl_merge_partials(part_o.data_ptr(), part_lse.data_ptr(), plan.plan_hdr.data_ptr(),
-                                     plan.tile_indptr.data_ptr(), rows, Hq, Hkv, D, code, out.data_ptr(), st)
+                                     plan.tile_indptr.data_ptr(), plan.cta_first_seq.data_ptr(), plan.n_ctas,
+                                     rows, Hq, Hkv, D, code, out.data_ptr(), st)
         _lib.check(rc, "bsgl_merge_partials")
         _count()
     return out

@@ -141,10 +141,12 @@ int bsgl_paged_attention(const void* q, const void* k_slab, const void* v_slab,
                          float* part_o, float* part_lse, int n_ctas, void* stream);
 
 /* K2c.  LSE merge of the partials of every sequence that was split; rows with no KV tokens
- * get zeros.  Must follow bsgl_paged_attention on the same stream with the same plan. */
+ * get zeros.  Must follow bsgl_paged_attention on the same stream with the same plan and n_ctas
+ * (one CTA per plan boundary x 4 q heads: at most n_ctas-1 sequences are split). */
 int bsgl_merge_partials(const float* part_o, const float* part_lse, const int32_t* plan_hdr,
-                        const int32_t* tile_indptr, int n_rows, int n_q_heads, int n_kv_heads,
-                        int head_dim, int dtype, void* out, void* stream);
+                        const int32_t* tile_indptr, const int32_t* cta_first_seq, int n_ctas,
+                        int n_rows, int n_q_heads, int n_kv_heads, int head_dim, int dtype, void* out,
+                        void* stream);
 
 /* K3.  Ragged extend attention (radix-cache prefix + new tokens) on tcgen05/TMEM tensor cores.
  * q rows are packed in request order (qo_indptr); request i's row r sees KV columns

@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--layers", type=int, default=2)
     ap.add_argument("--n-ctas", type=int, default=0)
+    ap.add_argument("--no-merge", action="store_true", help="time K2 alone (skip the K2c merge launch)")
     ap.add_argument("--sequential", action="store_true", help="unfragmented page table (slots in order)")
     a = ap.parse_args()
     Hq, Hkv, D = GEOM[a.geom]
@@ -48,20 +49,20 @@ def main():
     ws = ops.partial_buffers(dev, md.plan.n_ctas, Hq, Hkv, D)
     scale = D ** -0.5
     for i in range(3):
-        ops.paged_attention(q, *slabs[i % a.layers], r2t, md.plan, scale, workspace=ws)
+        ops.paged_attention(q, *slabs[i % a.layers], r2t, md.plan, scale, workspace=ws, merge=not a.no_merge)
     torch.cuda.synchronize()
     e0 = [torch.cuda.Event(enable_timing=True) for _ in range(a.iters)]
     e1 = [torch.cuda.Event(enable_timing=True) for _ in range(a.iters)]
     for i in range(a.iters):
         e0[i].record()
-        ops.paged_attention(q, *slabs[i % a.layers], r2t, md.plan, scale, workspace=ws)
+        ops.paged_attention(q, *slabs[i % a.layers], r2t, md.plan, scale, workspace=ws, merge=not a.no_merge)
         e1[i].record()
     torch.cuda.synchronize()
     ms = sorted(x.elapsed_time(y) for x, y in zip(e0, e1))
     tot = int(seq.sum().item())
     bytes_ = tot * Hkv * D * 2 * 2 + 4 * tot + 2 * a.batch * Hq * D * 2
     med = ms[len(ms) // 2]
-    print(json.dumps({"geom": a.geom, "batch": a.batch, "ctx": a.ctx, "ragged": a.ragged, "sequential": a.sequential, "ms_med": med,
+    print(json.dumps({"geom": a.geom, "batch": a.batch, "ctx": a.ctx, "ragged": a.ragged, "sequential": a.sequential, "merge": not a.no_merge, "ms_med": med,
                       "ms_min": ms[0], "GBps_med": bytes_ / med / 1e6, "GBps_best": bytes_ / ms[0] / 1e6,
                       "frac_of_6524.6": bytes_ / med / 1e6 / 6524.6, "bytes": bytes_,
                       "plan_hdr": md.plan.plan_hdr.tolist()}))
