@@ -71,6 +71,9 @@ __global__ void __launch_bounds__(256) kv_store_kernel(DstT* __restrict__ k_slab
                                                        int n_kv_heads, int head_dim, int64_t k_row_stride,
                                                        int64_t k_head_stride, int64_t v_row_stride,
                                                        int64_t v_head_stride) {
+  // the attention kernel behind us is a programmatic dependent: let it launch and set up while the rows land
+  // (it reads nothing before its griddepcontrol.wait, which returns once this grid has completed)
+  asm volatile("griddepcontrol.launch_dependents;");
   const int chunks_per_head = head_dim >> 3;                 // 8 elements (16 B of 16-bit dst) per chunk
   const int chunks_per_row = n_kv_heads * chunks_per_head;   // per K (or V) row
   const int64_t total = n_tokens * 2 * chunks_per_row;

@@ -86,14 +86,6 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
   constexpr int NSUB = C::NSUB;
   constexpr int KS = D / 16;   // k-steps of QK^T == m-tiles of PV
 
-  const int n_tiles = plan_hdr[0];
-  const int n_eff = plan_hdr[1];
-  const int n_seqs = plan_hdr[2];
-  const int cta = blockIdx.x;
-  if (cta >= n_eff || n_tiles == 0) return;
-
-  // the merge kernel behind us is a programmatic dependent: let it launch and park at its griddepcontrol.wait
-  asm volatile("griddepcontrol.launch_dependents;");
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* stages = smem;
   float* scratch = reinterpret_cast<float*>(smem + NST * C::STAGE_BYTES);
@@ -118,6 +110,18 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
     fence_mbar_init();
     fence_proxy_async_smem();
   }
+
+  // Programmatic dependent launch, both ways.  This kernel is launched as a dependent of whatever precedes it
+  // on the stream (K1 kv_store triggers at its start): launch, CTA placement and the barrier set-up above
+  // overlap that kernel; nothing it may have written (KV rows, q, the plan) is read before this wait.  The
+  // merge kernel behind us is in turn our dependent: let it launch and park at its own wait.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;");
+  const int n_tiles = plan_hdr[0];
+  const int n_eff = plan_hdr[1];
+  const int n_seqs = plan_hdr[2];
+  const int cta = blockIdx.x;
+  if (cta >= n_eff || n_tiles == 0) return;
 
   const int tile_lo = cta_tile_begin(cta, n_tiles, n_eff);
   const int tile_hi = cta_tile_begin(cta + 1, n_tiles, n_eff);
@@ -407,9 +411,19 @@ static int launch_paged_attention(const void* q, const void* k_slab, const void*
     configured_dev = dev;
   }
   const float scale_log2 = sm_scale * 1.4426950408889634f;
-  kern<<<n_ctas, kThreads, C::SMEM_BYTES, stream>>>((const T*)q, (const T*)k_slab, (const T*)v_slab, idx_base,
-                                                    row_idx_off, row_kv_len, plan_hdr, tile_indptr, cta_first_seq,
-                                                    n_q_heads, n_kv_heads, scale_log2, (T*)out, part_o, part_lse);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)n_ctas);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = C::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  BSGL_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, (const T*)q, (const T*)k_slab, (const T*)v_slab, idx_base, row_idx_off,
+                                   row_kv_len, plan_hdr, tile_indptr, cta_first_seq, n_q_heads, n_kv_heads,
+                                   scale_log2, (T*)out, part_o, part_lse));
   return check_launch("paged_attention_kernel");
 }
 

@@ -50,6 +50,7 @@ __global__ void __launch_bounds__(kRopeThreads) rope_kv_store_kernel(
     const float* __restrict__ inv_freq, const int32_t* __restrict__ loc, T* __restrict__ k_slab,
     T* __restrict__ v_slab, T* __restrict__ q_out, int n_q_heads, int n_kv_heads, int head_dim) {
   extern __shared__ float cs[];                  // cos[D/2], sin[D/2]
+  asm volatile("griddepcontrol.launch_dependents;");   // the attention kernel may launch and set up meanwhile
   const int half = head_dim >> 1;
   const int64_t t = blockIdx.x;
   const float pos = (float)positions[t];         // positions.float()
