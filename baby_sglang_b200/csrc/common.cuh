@@ -80,8 +80,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   return ok != 0;
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+#ifdef BSGL_DEBUG_SPIN
+  // debugging aid (-DBSGL_DEBUG_SPIN): name the stuck waiter instead of hanging the GPU
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins == (1u << 22)) {
+      printf("[bsgl] stuck: cta %d thread %d bar@%u parity %u\n", (int)blockIdx.x, (int)threadIdx.x, bar, parity);
+      __trap();
+    }
+  }
+#else
   while (!mbar_try_wait(bar, parity)) {
   }
+#endif
 }
 
 // TMA row gather: one contiguous global row -> shared, completion counted on an mbarrier (UBLKCP).

@@ -59,6 +59,14 @@ struct Cfg {
   static constexpr int NR = kTile / RSTEP;                  // rows per producer thread per tile
   static constexpr int PD_RAW = 16 / NR;                    // page-table prefetch distance in tiles
   static constexpr int PD = PD_RAW < 2 ? 2 : (PD_RAW > 8 ? 8 : PD_RAW);
+  // Narrow rows (one KV head per group, 256 B): a tile is only 8 KB, i.e. ~360 clk of HBM time per SM, less than
+  // the dependent-issue latency of one producer iteration (~84 instructions per warp per tile, measured with
+  // ncu).  There each producer WARP takes every 4th tile on its own (WPT): 4 tiles are being issued at once and
+  // the per-tile bookkeeping is paid by one warp instead of four.
+  static constexpr bool WPT = ROW_BYTES <= 256;
+  static constexpr int RPI = 512 / ROW_BYTES;               // WPT: rows covered by one warp instruction
+  static constexpr int NI = RPI > 0 ? kTile / RPI : 0;      // WPT: instructions per K (or V) tile
+  static constexpr int FULL_ARRIVALS = WPT ? 32 : kProducerThreads;
   static_assert(CPR <= kProducerThreads && kProducerThreads % CPR == 0 && kTile % RSTEP == 0 && NR >= 1,
                 "row width does not map onto the producer threads");
   static constexpr int DP = D + 4;                        // scratch row pitch in floats
@@ -68,7 +76,11 @@ struct Cfg {
   static constexpr int ITEM_BYTES = kMaxItems * (int)sizeof(Item);
   static constexpr int FIXED_BYTES = SCR_BYTES + ML_BYTES + ITEM_BYTES + 1024 /*barriers + slack*/;
   static constexpr int NSTAGES_RAW = (kSmemBudget - FIXED_BYTES) / STAGE_BYTES;
-  static constexpr int NSTAGES = NSTAGES_RAW > 24 ? 24 : NSTAGES_RAW;
+  static constexpr int NSTAGES_CAP = NSTAGES_RAW > 24 ? 24 : NSTAGES_RAW;
+  // WPT: a stage must belong to the same producer warp in every round (NSTAGES % 4 == 0).  Otherwise the warp
+  // owning round r+1 of a stage can run two rounds ahead of the warp owning round r, and its parity wait on the
+  // empty barrier passes on the stale phase (seen as a hang at full load, never in the small parity cases).
+  static constexpr int NSTAGES = WPT ? (NSTAGES_CAP / kProducerWarps) * kProducerWarps : NSTAGES_CAP;
   static constexpr int SMEM_BYTES = NSTAGES * STAGE_BYTES + FIXED_BYTES;
   static_assert(NSTAGES >= 3, "not enough shared memory for the KV ring");
 };
@@ -104,7 +116,7 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NST; ++s) {
-      mbar_init(full_bar0 + 8 * s, kProducerThreads);   // one cp.async-completion arrive per producer thread
+      mbar_init(full_bar0 + 8 * s, C::FULL_ARRIVALS);   // one cp.async-completion arrive per issuing thread
       mbar_init(empty_bar0 + 8 * s, HPB);    // one arrive per consumer warp of the owning sub-group
     }
     fence_mbar_init();
@@ -160,7 +172,8 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
       // (narrow rows), and it carries across item boundaries.
       const int p = threadIdx.x - kConsumerWarps * 32;
       const int col = p % C::CPR;             // this thread's 16-byte column of every row it copies
-      const int r0 = p / C::CPR;              // first row; then every RSTEP-th
+      // first row, then every RSTEP-th; WPT: the tile token whose page-table entry this lane fetches
+      const int r0 = C::WPT ? (lane & 15) : p / C::CPR;
       const uint32_t dst0 = stages_u32 + r0 * C::ROW_PITCH + col * 16;
       constexpr int PD = C::PD;
 
@@ -188,11 +201,82 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
           load_item(c);
         }
       };
-      Cursor pf;
-      pf.ii = 0;
-      load_item(pf);
-      Cursor is = pf;
-      int ring[PD][C::NR];
+      if constexpr (C::WPT) {
+        const int pw = warp - kConsumerWarps;              // this warp owns tiles with (tile counter % 4) == pw
+        const int rsub = lane / C::CPR;                    // row inside one warp instruction
+        constexpr int PDW = 4;                             // own tiles of page-table prefetch (= 16 tiles ahead)
+        auto advance_n = [&](Cursor& c, int n) {
+          while (n > 0 && c.ii < n_items) {
+            const int left = c.ntile - c.ti;
+            if (n < left) {
+              c.ti += n;
+              c.tok0 += n * kTile;
+              n = 0;
+            } else {
+              n -= left;
+              ++c.ii;
+              load_item(c);
+            }
+          }
+        };
+        Cursor pf;
+        pf.ii = 0;
+        load_item(pf);
+        const int skip = (pw - (int)stage_ctr) & 3;
+        advance_n(pf, skip);
+        Cursor is = pf;
+        uint32_t sc = stage_ctr + skip;
+        int ring[PDW];
+#pragma unroll
+        for (int u = 0; u < PDW; ++u) {
+          ring[u] = 0;
+          if (pf.ii < n_items) {
+            ring[u] = __ldg(pf.idxp + min(pf.tok0, pf.last_tok));
+            advance_n(pf, kProducerWarps);
+          }
+        }
+        const uint32_t dstw = stages_u32 + rsub * C::ROW_PITCH + col * 16;
+        while (is.ii < n_items) {
+#pragma unroll
+          for (int u = 0; u < PDW; ++u) {
+            if (is.ii >= n_items) break;
+            const int idx_tile = ring[u];
+            if (pf.ii < n_items) {
+              ring[u] = __ldg(pf.idxp + min(pf.tok0, pf.last_tok));
+              advance_n(pf, kProducerWarps);
+            }
+            const int64_t head_off = (int64_t)is.hg * HPB * D + col * 8;
+            const T* kb = k_slab + head_off;
+            const T* vb = v_slab + head_off;
+            const uint32_t st = sc % NST;
+            const uint32_t ph = (sc / NST) & 1;
+            mbar_wait(empty_bar0 + 8 * st, ph ^ 1);
+            const uint32_t dst = dstw + st * C::STAGE_BYTES;
+#pragma unroll
+            for (int i = 0; i < C::NI; ++i) {
+              const int idx = __shfl_sync(0xffffffffu, idx_tile, i * C::RPI + rsub);
+              const int64_t off = (int64_t)idx * slab_row;
+              cp_async16(dst + i * C::RPI * C::ROW_PITCH, kb + off);
+              cp_async16(dst + i * C::RPI * C::ROW_PITCH + C::KV_BYTES, vb + off);
+            }
+            cp_async_mbar_arrive(full_bar0 + 8 * st);
+            sc += kProducerWarps;
+            advance_n(is, kProducerWarps);
+          }
+        }
+        // every warp leaves the pass with the same tile counter
+        int nt = 0;
+        for (int i = lane; i < n_items; i += 32)
+          if (items[i].valid) nt += (items[i].tok_end - items[i].tok_begin + kTile - 1) / kTile;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) nt += __shfl_xor_sync(0xffffffffu, nt, o);
+        stage_ctr += nt;
+      } else {
+        Cursor pf;
+        pf.ii = 0;
+        load_item(pf);
+        Cursor is = pf;
+        int ring[PD][C::NR];
 #pragma unroll
       for (int u = 0; u < PD; ++u) {
         if (pf.ii < n_items) {
@@ -231,6 +315,7 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
           advance(is);
         }
       }
+      }   // !WPT
     } else {
       // ================================================================ consumer warps
       const int h = warp % HPB;        // KV head inside the group

@@ -200,6 +200,21 @@ def test_split_count_invariance(ops):
         assert (o - outs[0]).abs().max().item() <= 2 ** -6
 
 
+@pytest.mark.parametrize("Hq,Hkv,D", [(5, 1, 128), (4, 2, 64), (8, 1, 64)])
+def test_narrow_rows_many_items_per_cta(ops, Hq, Hkv, D):
+    """Rows of <= 256 B take the warp-per-tile producers (K2, Cfg::WPT).  200 ragged sequences on 1, 2 and 148 CTAs:
+    with 1-2 CTAs a CTA walks more than kMaxItems (64) sequences, so the tile counter carries across passes and the
+    tile -> warp assignment starts at every residue."""
+    g = torch.Generator().manual_seed(Hq * 100 + D)
+    seq = torch.randint(1, 200, (200,), generator=g).tolist()
+    seq[7], seq[100] = 1500, 16
+    c = make_paged_case(B=200, Hq=Hq, Hkv=Hkv, D=D, seq_lens=seq, seed=11)
+    ref = O.decode_attention(c.q.float(), *_stored(c), c.req_to_token, c.req_pool_indices, c.seq_lens)
+    for n in (1, 2, 148):
+        out, *_ = _run_backend(ops, c, n_ctas=n)
+        assert (out.float().cpu() - ref).abs().max().item() <= TOL, n
+
+
 def _stored(c):
     ks, vs = c.k_slab.float().clone(), c.v_slab.float().clone()
     O.kv_store(ks, vs, c.out_cache_loc, c.k.float(), c.v.float())
