@@ -273,9 +273,15 @@ def run_b200(args, rank, world, device):
     if with_oproj:   # this rank's column shard of o_proj (bias-free, qwen2.py:166): partial sums are exact
         w_o = torch.randn(w["hidden"], Hq * D, device=device, dtype=dt) * 0.02
 
+    fused_comm = None
+    if tp and args.oproj == "fused":   # K8: one kernel per rank instead of GEMM + NCCL call
+        fused_comm = tp_runtime.FusedOProjAllReduce(rank, world, tp_group, hidden=w["hidden"], max_tokens=B)
+
     def after_attention(out):
         if not with_oproj:
             return out
+        if fused_comm is not None:
+            return fused_comm(out, w_o)
         partial = torch.nn.functional.linear(out, w_o)
         return tp_runtime.tp_all_reduce_sum(partial, tp_group) if tp else partial
     # per-layer activations of one step, device-resident (for `value`) and pinned host copies (for `e2e`)
@@ -398,6 +404,9 @@ def run_b200(args, rank, world, device):
         allreduce = {"bytes": nbytes, "avg_ms": round(ar_ms, 5),
                      "busbw_GBps": round(2 * (world - 1) / world * nbytes / ar_ms / 1e6, 1),
                      "backend": "NCCL over NVLink/NVSwitch (torch.distributed all_reduce SUM)"}
+    used_fused = fused_comm is not None
+    if used_fused:
+        fused_comm.close()      # collective (barrier): every rank, before the others leave
     if rank != 0:
         return
     cpu = cpu_baseline(args.workload, seconds=12.0)
@@ -414,7 +423,9 @@ def run_b200(args, rank, world, device):
                                f"batch {B}{'' if tp else '/GPU'}, "
                                f"ctx {WORKLOADS[args.workload][2]}..{WORKLOADS[args.workload][3]}, page_size 1, "
                                f"{L} layers/step, fragmented page table",
-                   "parallelism": (f"KV-head TP x{world}: o_proj partial + NCCL all-reduce per layer" if tp else
+                   "parallelism": (f"KV-head TP x{world}: o_proj partial + "
+                                   + ("all-reduce fused in one kernel over NVLink peer memory (K8)" if used_fused
+                                      else "NCCL all-reduce per layer") if tp else
                                    "request-batch DP (no collective)" if world > 1 else "single GPU"),
                    "l2": f"inputs > L2: {k_bytes / 1e9:.2f} GB of KV per layer, {L} distinct layers per step",
                    "step": "K4 metadata + per layer (K1 kv_store, K2 paged attention, K2c merge"
@@ -434,6 +445,9 @@ def run_b200(args, rank, world, device):
         "extend_roofline": extend,
         "cpu_baseline": cpu,
     }
+    if used_fused:
+        line["oproj"] = {"impl": "K8 oproj_allreduce_kernel (tcgen05 GEMM + owner-reduce over NVLink peer memory)",
+                         "replaces": "F.linear + NCCL all-reduce (bench.py --oproj nccl)"}
     print(json.dumps(line), flush=True)
 
 
@@ -517,6 +531,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="ns", choices=sorted(WORKLOADS))
+    ap.add_argument("--oproj", default="fused", choices=["fused", "nccl"],
+                    help="c5 under TP: K8 (o_proj GEMM with the all-reduce fused over NVLink peer memory) or "
+                         "F.linear + NCCL all-reduce")
     ap.add_argument("--traffic", type=float, default=None,
                     help="dram bytes per launch of the dominant kernel from an ncu --set full capture (profiles/)")
     args = ap.parse_args()
