@@ -243,6 +243,45 @@ def shard_attention_heads(model: torch.nn.Module, rank: int, world_size: int, tp
     return plan
 
 
+def _mlp_modules(model: torch.nn.Module):
+    """Every module shaped like the reference's Qwen2MLP (qwen2.py:198-211): a fused `gate_up_proj.gate_up_proj`
+    linear of 2*I rows ([gate | up], split by `chunk(2)` at qwen2.py:221) and a bias-free `down_proj`."""
+    for m in model.modules():
+        inner = getattr(getattr(m, "gate_up_proj", None), "gate_up_proj", None)
+        if isinstance(inner, torch.nn.Linear) and isinstance(getattr(m, "down_proj", None), torch.nn.Linear):
+            yield m
+
+
+def shard_mlp(model: torch.nn.Module, rank: int, world_size: int, tp_group) -> int:
+    """Tensor-parallel SwiGLU MLP (second half), on the unchanged model: rank r keeps
+    intermediate columns [r*I/t, (r+1)*I/t) -- rows `cat(gate_shard, up_shard)` of the fused gate/up weight, so the
+    reference's `chunk(2, dim=-1)` (qwen2.py:221) still separates gate from up -- and the matching input columns of
+    `down_proj` (bias-free, qwen2.py:206), whose partial output is SUM all-reduced by a forward hook.  Returns the
+    per-rank intermediate size (0 if nothing was sharded: world 1, no MLP modules, or I % world != 0)."""
+    if world_size <= 1:
+        return 0
+    per_rank = 0
+    for m in _mlp_modules(model):
+        lin, down = m.gate_up_proj.gate_up_proj, m.down_proj
+        inter = down.in_features
+        if inter % world_size or lin.out_features != 2 * inter:
+            return 0
+        per_rank = inter // world_size
+        lo, hi = rank * per_rank, (rank + 1) * per_rank
+        rows = torch.cat([torch.arange(lo, hi), inter + torch.arange(lo, hi)]).to(lin.weight.device)
+        with torch.no_grad():
+            lin.weight = torch.nn.Parameter(lin.weight.index_select(0, rows).contiguous(), requires_grad=False)
+            if lin.bias is not None:
+                lin.bias = torch.nn.Parameter(lin.bias.index_select(0, rows).contiguous(), requires_grad=False)
+            lin.out_features = 2 * per_rank
+            down.weight = torch.nn.Parameter(down.weight[:, lo:hi].contiguous(), requires_grad=False)
+            down.in_features = per_rank
+        if hasattr(m.gate_up_proj, "intermediate_size"):
+            m.gate_up_proj.intermediate_size = per_rank
+        down.register_forward_hook(lambda _mod, _inp, out, g=tp_group: tp_all_reduce_sum(out, g))
+    return per_rank
+
+
 def _fused_oproj_forward(o_proj: torch.nn.Linear, comm: "FusedOProjAllReduce", tp_group):
     """`o_proj.forward` replacement: K8 for batches the communicator was sized for, the NCCL pair otherwise."""
     def forward(x: torch.Tensor) -> torch.Tensor:

@@ -101,6 +101,19 @@ def _body_kv_head_tp(tp, rank, world, group):
     tr = greedy_generate(sharded, st, prompts, 12, torch.device("cpu"), torch.float32)
     assert tr.pools[1].head_num == 1         # per-rank KV pool holds Hkv / t heads
     assert tr.ids == want, f"rank {rank}: TP token ids differ"
+    # ... and with the MLP sharded too (gate/up rows + down_proj columns, all-reduce after down_proj)
+    assert tp.shard_mlp(sharded, rank, world, group) == cfg.intermediate_size // world
+    mlp = sharded.model.layers[0].mlp
+    assert mlp.gate_up_proj.gate_up_proj.weight.shape == (cfg.intermediate_size, cfg.hidden_size)   # 2 * I / 2 rows
+    assert mlp.down_proj.weight.shape == (cfg.hidden_size, cfg.intermediate_size // world)
+    ref_mlp = full.model.layers[0].mlp
+    lo = rank * (cfg.intermediate_size // world)
+    assert torch.equal(mlp.gate_up_proj.gate_up_proj.weight[0], ref_mlp.gate_up_proj.gate_up_proj.weight[lo])
+    assert torch.equal(mlp.gate_up_proj.gate_up_proj.weight[cfg.intermediate_size // world],
+                       ref_mlp.gate_up_proj.gate_up_proj.weight[cfg.intermediate_size + lo])
+    tr2 = greedy_generate(sharded, st, prompts, 12, torch.device("cpu"), torch.float32)
+    assert tr2.ids == want, f"rank {rank}: TP (attention + MLP) token ids differ"
+    assert tp.shard_mlp(full, rank, 1, None) == 0
 
 
 def _body_dp_plan(tp, rank, world, group):
