@@ -215,6 +215,28 @@ def test_narrow_rows_many_items_per_cta(ops, Hq, Hkv, D):
         assert (out.float().cpu() - ref).abs().max().item() <= TOL, n
 
 
+@pytest.mark.parametrize("n_ctas", [1, 3, 148])
+def test_rows_without_kv_tokens_are_zero(ops, n_ctas):
+    """A row whose KV length is 0 owns no tile, so no attention CTA writes it: the merge launch zero-fills it
+    (K2c's zero-fill CTAs) and leaves every other row alone.  (The reference never decodes an empty request; the
+    row-wise extend plan and padded batches can produce such rows.)"""
+    c = make_paged_case(B=6, Hq=12, Hkv=2, D=128, seq_lens=[300, 1, 77, 513, 40, 9], seed=4)
+    ref = O.decode_attention(c.q.float(), *_stored(c), c.req_to_token, c.req_pool_indices, c.seq_lens)
+    k_slab, v_slab = (t.to(torch.bfloat16).cuda() for t in _stored(c))
+    seq = c.seq_lens.clone()
+    seq[1] = 0
+    seq[4] = 0
+    md = ops.build_decode_metadata(c.req_to_token.cuda(), c.req_pool_indices.cuda(), seq.cuda(), c.Hkv, n_ctas=n_ctas)
+    out = torch.full((6, 12 * 128), 7.0, dtype=torch.bfloat16, device="cuda")
+    ops.paged_attention(c.q.to(torch.bfloat16).cuda(), k_slab, v_slab, c.req_to_token.cuda(), md.plan, 128 ** -0.5,
+                        out=out)
+    torch.cuda.synchronize()
+    out = out.float().cpu()
+    assert torch.count_nonzero(out[1]) == 0 and torch.count_nonzero(out[4]) == 0
+    keep = [0, 2, 3, 5]
+    assert (out[keep] - ref[keep]).abs().max().item() <= TOL
+
+
 def _stored(c):
     ks, vs = c.k_slab.float().clone(), c.v_slab.float().clone()
     O.kv_store(ks, vs, c.out_cache_loc, c.k.float(), c.v.float())
