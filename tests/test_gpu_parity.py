@@ -237,6 +237,61 @@ def test_rows_without_kv_tokens_are_zero(ops, n_ctas):
     assert (out[keep] - ref[keep]).abs().max().item() <= TOL
 
 
+def test_decode_step_is_cuda_graph_capturable(ops):
+    """K4 + per layer (K1, K2, K2c) make no host sync and take all sizes from device buffers, so a whole decode step
+    -- programmatic dependent launches included -- captures into one CUDA graph.  Replaying it after the batch moved
+    on (new seq_lens / slots / q, k, v written into the same buffers) must give what eager launches give."""
+    L = 2
+    c = make_paged_case(B=5, Hq=28, Hkv=4, D=128, seq_lens=[700, 33, 1500, 16, 255], seed=8)
+    dev = torch.device("cuda")
+    r2t = c.req_to_token.cuda()
+    rpi = c.req_pool_indices.cuda()
+    seq = (c.seq_lens - 1).cuda()                        # static buffers, updated in place between replays
+    loc = c.out_cache_loc.cuda().clone()
+    slabs = [(c.k_slab.to(torch.bfloat16).cuda().clone(), c.v_slab.to(torch.bfloat16).cuda().clone()) for _ in range(L)]
+    T = c.qkv.shape[0]
+    qkv = c.qkv.to(torch.bfloat16).cuda().clone()
+    outs = [torch.empty(T, 28 * 128, dtype=torch.bfloat16, device=dev) for _ in range(L)]
+
+    def step():
+        q, k, v = qkv.split([28 * 128, 4 * 128, 4 * 128], dim=-1)
+        q = q.contiguous().view(T, 28, 128)
+        k = k.contiguous().view(T, 4, 128)
+        v = v.view(T, 4, 128)
+        md = ops.build_decode_metadata(r2t, rpi, seq, 4)
+        for l in range(L):
+            ops.kv_store(slabs[l][0], slabs[l][1], loc, k, v)
+            ops.paged_attention(q, slabs[l][0], slabs[l][1], r2t, md.plan, 128 ** -0.5, out=outs[l])
+
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        step()                                             # warm-up outside capture (function attributes, allocator)
+    side.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=side):
+        step()
+    # the batch moves on: one more token per request, written into the SAME buffers
+    seq.add_(1)
+    qkv.copy_(torch.randn(qkv.shape, generator=torch.Generator().manual_seed(99)).to(torch.bfloat16))
+    graph.replay()
+    torch.cuda.synchronize()
+    got = [o.clone() for o in outs]
+    for o in outs:
+        o.zero_()
+    step()                                                 # eager, same inputs (the stores are idempotent)
+    torch.cuda.synchronize()
+    for l in range(L):
+        assert torch.equal(got[l], outs[l]), f"layer {l}: graph replay differs from eager launches"
+    # and it is the right answer for the moved-on batch
+    q, k, v = qkv.cpu().float().split([28 * 128, 4 * 128, 4 * 128], dim=-1)
+    ks, vs = c.k_slab.float().clone(), c.v_slab.float().clone()
+    O.kv_store(ks, vs, c.out_cache_loc, k.reshape(T, 4, 128).to(torch.bfloat16).float(),
+               v.reshape(T, 4, 128).to(torch.bfloat16).float())
+    ref = O.decode_attention(q.reshape(T, 28, 128), ks.to(torch.bfloat16).float(), vs.to(torch.bfloat16).float(),
+                             c.req_to_token, c.req_pool_indices, c.seq_lens)
+    assert (got[0].float().cpu() - ref).abs().max().item() <= TOL
+
+
 def _stored(c):
     ks, vs = c.k_slab.float().clone(), c.v_slab.float().clone()
     O.kv_store(ks, vs, c.out_cache_loc, c.k.float(), c.v.float())
