@@ -108,8 +108,8 @@ __device__ __forceinline__ void reduce_owned_tile(const OprojComm& comm, const u
       const int item = (it0 + u) * 128 + etid;
       const int c = item & 15, r = item >> 4;                // 16 lanes cover one 256-byte output row segment
 #pragma unroll
-      for (int s = 0; s < W; ++s)
-        if (s < world) v[u][s] = __ldcg(reinterpret_cast<const uint4*>(part0 + s * src_stride) + c * 128 + r);
+      for (int s = 0; s < W; ++s)   // unconditional (a source past `world` re-reads source 0 and is not summed):
+        v[u][s] = __ldcg(reinterpret_cast<const uint4*>(part0 + (s < world ? s : 0) * src_stride) + c * 128 + r);
     }
 #pragma unroll
     for (int u = 0; u < IPB; ++u) {
@@ -154,7 +154,7 @@ __device__ __forceinline__ void reduce_owned_tile(const OprojComm& comm, const u
 template <typename T>
 __global__ void __launch_bounds__(kOpThreads, 1)
 oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
-                       const OprojComm comm, int M, int N, int K, int rank, int world, int max_slots,
+                       const __grid_constant__ OprojComm comm, int M, int N, int K, int rank, int world, int max_slots,
                        int64_t out_parity_bytes, uint32_t epoch) {
   extern __shared__ uint8_t smem_dyn[];
   const uint32_t raw = smem_u32(smem_dyn);
