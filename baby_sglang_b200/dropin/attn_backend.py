@@ -40,6 +40,7 @@ class SimpleAttentionBackend:
                                                pool.head_num)
             forward_batch.attn_metadata = md
             forward_batch.qo_indptr, forward_batch.kv_indptr = md.qo_indptr, md.kv_indptr
+        md.use_on_current_stream()     # overlap mode: built on the scheduler's stream, consumed on the worker's
         return md
 
     @staticmethod

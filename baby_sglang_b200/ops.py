@@ -180,6 +180,27 @@ class BatchMetadata:
     plan: Optional[AttnPlan]
     kv_indices: Optional[torch.Tensor] = None  # int32 [sum(seq)] (built on request)
     heavy_order: Optional[torch.Tensor] = None  # int32 [B] requests by descending seq_len (extend only)
+    _streams_seen: Optional[set] = None         # streams the buffers are already recorded on
+
+    def use_on_current_stream(self) -> None:
+        """The reference's overlap worker builds the batch on the scheduler thread's stream and runs the forward on
+        another one (overlap_worker.py:83-106).  torch's caching allocator only knows the allocating stream, so a
+        buffer released right after the launches were enqueued could be handed out again while the kernels still
+        read it: record every buffer on the consuming stream, once per stream."""
+        cur = torch.cuda.current_stream()
+        key = cur.cuda_stream
+        if self._streams_seen is None:
+            self._streams_seen = set()
+        if key in self._streams_seen:
+            return
+        self._streams_seen.add(key)
+        tensors = [self.positions, self.kv_indptr, self.qo_indptr, self.extended_lens, self.kv_indices, self.heavy_order]
+        if self.plan is not None:
+            tensors += [self.plan.row_idx_off, self.plan.row_kv_len, self.plan.plan_hdr, self.plan.tile_indptr,
+                        self.plan.cta_first_seq]
+        for t in tensors:
+            if t is not None and t.is_cuda:
+                t.record_stream(cur)
 
 
 def _plan_buffers(dev, n_rows: int, nhg: int, n_ctas: int):
