@@ -129,16 +129,18 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
   // merge kernel behind us is in turn our dependent: let it launch and park at its own wait.
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;");
+  const int cta = blockIdx.x;
   const int n_tiles = plan_hdr[0];
   const int n_eff = plan_hdr[1];
   const int n_seqs = plan_hdr[2];
-  const int cta = blockIdx.x;
+  // read with the header, not after the early exit: one round trip less on the kernel's start-up chain
+  // (cta_first_seq has gridDim.x + 1 entries whatever n_eff is)
+  const int seq_first = cta_first_seq[cta];
+  int seq_last = cta_first_seq[cta + 1];
   if (cta >= n_eff || n_tiles == 0) return;
 
   const int tile_lo = cta_tile_begin(cta, n_tiles, n_eff);
   const int tile_hi = cta_tile_begin(cta + 1, n_tiles, n_eff);
-  const int seq_first = cta_first_seq[cta];
-  int seq_last = cta_first_seq[cta + 1];
   if (seq_last > n_seqs - 1) seq_last = n_seqs - 1;
 
   uint32_t stage_ctr = 0;   // running tile counter of this CTA; identical in every warp
