@@ -79,41 +79,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Bounded wait: a protocol bug must trap (the launch fails with an error the host sees), never hang the GPU.
+// 2^28 failed polls is seconds -- far beyond any legitimate wait on these barriers.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-#ifdef BSGL_DEBUG_SPIN
-  // debugging aid (-DBSGL_DEBUG_SPIN): name the stuck waiter instead of hanging the GPU
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins == (1u << 22)) {
+    if (++spins == (1u << 28)) {
+#ifdef BSGL_DEBUG_SPIN
       printf("[bsgl] stuck: cta %d thread %d bar@%u parity %u\n", (int)blockIdx.x, (int)threadIdx.x, bar, parity);
+#endif
       __trap();
     }
   }
-#else
-  while (!mbar_try_wait(bar, parity)) {
-  }
-#endif
-}
-
-// TMA row gather: one contiguous global row -> shared, completion counted on an mbarrier (UBLKCP).
-__device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_smem),
-      "l"(src), "r"(bytes), "r"(bar)
-      : "memory");
-}
-__device__ __forceinline__ void bulk_g2s_hint(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t bar,
-                                              uint64_t policy) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
-          "r"(dst_smem),
-      "l"(src), "r"(bytes), "r"(bar), "l"(policy)
-      : "memory");
-}
-__device__ __forceinline__ uint64_t policy_evict_first() {
-  uint64_t p;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-  return p;
 }
 
 // 16-byte asynchronous global->shared copy, L2-only caching (LDGSTS.BYPASS).

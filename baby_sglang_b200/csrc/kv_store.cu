@@ -65,7 +65,7 @@ struct Cvt8<__nv_bfloat16, __half> {
 
 template <typename SrcT, typename DstT>
 __global__ void __launch_bounds__(256) kv_store_kernel(DstT* __restrict__ k_slab, DstT* __restrict__ v_slab,
-                                                       const int32_t* __restrict__ loc,
+                                                       int64_t n_slots, const int32_t* __restrict__ loc,
                                                        const SrcT* __restrict__ k_src,
                                                        const SrcT* __restrict__ v_src, int64_t n_tokens,
                                                        int n_kv_heads, int head_dim, int64_t k_row_stride,
@@ -87,6 +87,7 @@ __global__ void __launch_bounds__(256) kv_store_kernel(DstT* __restrict__ k_slab
     const int h = c / chunks_per_head;
     const int d = (c - h * chunks_per_head) << 3;
     const int64_t slot = (int64_t)loc[t];                    // int32 -> int64 widen
+    if ((uint64_t)slot >= (uint64_t)n_slots) __trap();       // the reference's index-put device-asserts here
     const SrcT* src = is_v ? v_src + t * v_row_stride + h * v_head_stride + d
                            : k_src + t * k_row_stride + h * k_head_stride + d;
     DstT* dst = (is_v ? v_slab : k_slab) + slot * slab_row + (int64_t)h * head_dim + d;
@@ -95,7 +96,7 @@ __global__ void __launch_bounds__(256) kv_store_kernel(DstT* __restrict__ k_slab
 }
 
 template <typename SrcT, typename DstT>
-static int launch_kv_store(void* k_slab, void* v_slab, const int32_t* loc, const void* k_src, const void* v_src,
+static int launch_kv_store(void* k_slab, void* v_slab, int64_t n_slots, const int32_t* loc, const void* k_src, const void* v_src,
                            int64_t n_tokens, int n_kv_heads, int head_dim, int64_t krs, int64_t khs, int64_t vrs,
                            int64_t vhs, cudaStream_t stream) {
   const int64_t total = n_tokens * 2 * n_kv_heads * (head_dim >> 3);
@@ -106,14 +107,14 @@ static int launch_kv_store(void* k_slab, void* v_slab, const int32_t* loc, const
   int64_t blocks = (total + 255) / 256;
   if (blocks > (int64_t)sms * 8) blocks = (int64_t)sms * 8;
   kv_store_kernel<SrcT, DstT><<<(unsigned)blocks, 256, 0, stream>>>(
-      (DstT*)k_slab, (DstT*)v_slab, loc, (const SrcT*)k_src, (const SrcT*)v_src, n_tokens, n_kv_heads, head_dim, krs,
+      (DstT*)k_slab, (DstT*)v_slab, n_slots, loc, (const SrcT*)k_src, (const SrcT*)v_src, n_tokens, n_kv_heads, head_dim, krs,
       khs, vrs, vhs);
   return check_launch("kv_store_kernel");
 }
 
 }  // namespace bsgl
 
-extern "C" int bsgl_kv_store(void* k_slab, void* v_slab, const int32_t* loc, const void* k_src, const void* v_src,
+extern "C" int bsgl_kv_store(void* k_slab, void* v_slab, int64_t n_slots, const int32_t* loc, const void* k_src, const void* v_src,
                              int64_t n_tokens, int n_kv_heads, int head_dim, int64_t k_row_stride,
                              int64_t k_head_stride, int64_t v_row_stride, int64_t v_head_stride, int src_dtype,
                              int slab_dtype, void* stream) {
@@ -121,6 +122,7 @@ extern "C" int bsgl_kv_store(void* k_slab, void* v_slab, const int32_t* loc, con
   BSGL_REQUIRE(n_tokens >= 0, "bsgl_kv_store: negative token count");
   if (n_tokens == 0) return BSGL_OK;
   BSGL_REQUIRE(k_slab && v_slab && loc && k_src && v_src, "bsgl_kv_store: null pointer");
+  BSGL_REQUIRE(n_slots > 0, "bsgl_kv_store: n_slots must be the slab's row count (S + 1)");
   BSGL_REQUIRE(n_kv_heads > 0 && head_dim > 0 && head_dim % 8 == 0, "bsgl_kv_store: head_dim must be a multiple of 8");
   BSGL_REQUIRE(slab_dtype == BSGL_BF16 || slab_dtype == BSGL_F16,
                "bsgl_kv_store: slab dtype must be bf16 or fp16 (fp8 KV cache is unimplemented in the reference too, "
@@ -135,7 +137,7 @@ extern "C" int bsgl_kv_store(void* k_slab, void* v_slab, const int32_t* loc, con
                "bsgl_kv_store: source strides must keep 16-byte alignment");
   cudaStream_t s = (cudaStream_t)stream;
 #define BSGL_KVS(S, D) \
-  return launch_kv_store<S, D>(k_slab, v_slab, loc, k_src, v_src, n_tokens, n_kv_heads, head_dim, k_row_stride, \
+  return launch_kv_store<S, D>(k_slab, v_slab, n_slots, loc, k_src, v_src, n_tokens, n_kv_heads, head_dim, k_row_stride, \
                                k_head_stride, v_row_stride, v_head_stride, s)
   if (slab_dtype == BSGL_BF16) {
     if (src_dtype == BSGL_BF16) BSGL_KVS(__nv_bfloat16, __nv_bfloat16);

@@ -24,8 +24,14 @@ __global__ void __launch_bounds__(kMergeWarps * 32) merge_partials_kernel(
   const int nhg = n_kv_heads / hpb;
   const int n_tiles = plan_hdr[0], n_eff = plan_hdr[1], n_seqs = plan_hdr[2];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // Programmatic dependent launch: EVERY thread of this grid executes griddepcontrol.wait before it exits or
+  // touches anything the attention kernel writes (PTX ISA: a dependent grid must wait when its prerequisite uses
+  // launch_dependents; otherwise this grid could retire -- and release the next kernel on the stream, which is
+  // ordered after THIS grid only -- while the attention kernel is still writing `out` and the partials).  The
+  // plan look-ups below read only buffers written before the attention kernel started, so they overlap its tail.
   if ((int)blockIdx.x >= n_bound) {
     // ---- rows with no KV tokens are defined as zeros (nobody else writes them)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     if (blockIdx.y != 0) return;
     const int j0 = ((int)blockIdx.x - n_bound) * kZeroSeqsPerCta;
     for (int j = j0 + threadIdx.x; j < min(j0 + kZeroSeqsPerCta, n_seqs); j += blockDim.x) {
@@ -38,22 +44,28 @@ __global__ void __launch_bounds__(kMergeWarps * 32) merge_partials_kernel(
   }
   const int b = blockIdx.x;
   const int head = blockIdx.y * kMergeWarps + warp;
-  if (b + 1 >= n_eff || head >= heads || n_tiles == 0) return;
-  const int t = cta_tile_begin(b + 1, n_tiles, n_eff);   // first tile of CTA b+1
-  const int j = cta_first_seq[b + 1];                    // the sequence that holds it
-  if (j >= n_seqs) return;
-  const int tb = tile_indptr[j], te = tile_indptr[j + 1];
-  if (tb >= t) return;                                   // starts at the boundary: not split here
-  const int c_first = cta_of_tile(tb, n_tiles, n_eff);
-  if (c_first != b) return;                              // an earlier boundary merges this sequence
-  const int c_last = cta_of_tile(te - 1, n_tiles, n_eff);
+  bool work = !(b + 1 >= n_eff || head >= heads || n_tiles == 0);
+  int j = 0, tb = 0, te = 0, c_first = 0, c_last = 0;
+  if (work) {
+    const int t = cta_tile_begin(b + 1, n_tiles, n_eff);   // first tile of CTA b+1
+    j = cta_first_seq[b + 1];                              // the sequence that holds it
+    work = j < n_seqs;
+    if (work) {
+      tb = tile_indptr[j], te = tile_indptr[j + 1];
+      work = tb < t;                                       // starts at the boundary: not split here
+    }
+    if (work) {
+      c_first = cta_of_tile(tb, n_tiles, n_eff);
+      work = c_first == b;                                 // an earlier boundary merges this sequence
+      c_last = cta_of_tile(te - 1, n_tiles, n_eff);
+    }
+  }
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (!work) return;
   const int row = j / nhg, hg = j - row * nhg;
   const int d = lane * 4;
   T* orow = out + ((int64_t)row * n_q_heads + (int64_t)hg * heads + head) * D;
   float m = -INFINITY, den = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-  // Programmatic dependent launch: everything above read only the plan (written before the attention kernel
-  // started) and overlapped that kernel's tail; its partials are visible after this wait.
-  asm volatile("griddepcontrol.wait;" ::: "memory");
 #pragma unroll 4
   for (int c = c_first; c <= c_last; ++c) {
     const int64_t slot = 2 * c + (c == c_first ? 1 : 0);

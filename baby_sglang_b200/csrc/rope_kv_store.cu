@@ -48,7 +48,7 @@ template <typename T>
 __global__ void __launch_bounds__(kRopeThreads) rope_kv_store_kernel(
     const T* __restrict__ qkv, int64_t row_stride, const int64_t* __restrict__ positions,
     const float* __restrict__ inv_freq, const int32_t* __restrict__ loc, T* __restrict__ k_slab,
-    T* __restrict__ v_slab, T* __restrict__ q_out, int n_q_heads, int n_kv_heads, int head_dim) {
+    T* __restrict__ v_slab, int64_t n_slots, T* __restrict__ q_out, int n_q_heads, int n_kv_heads, int head_dim) {
   extern __shared__ float cs[];                  // cos[D/2], sin[D/2]
   asm volatile("griddepcontrol.launch_dependents;");   // the attention kernel may launch and set up meanwhile
   const int half = head_dim >> 1;
@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(kRopeThreads) rope_kv_store_kernel(
   __syncthreads();
   const T* row = qkv + t * row_stride;
   const int64_t slot = loc ? (int64_t)loc[t] : 0;
+  if (loc && (uint64_t)slot >= (uint64_t)n_slots) __trap();   // the reference's index-put device-asserts here
   const int cph = half >> 3;                     // chunk pairs per rotated head
   const int n_rot = (n_q_heads + n_kv_heads) * cph;
   const int n_v = n_kv_heads * (head_dim >> 3);
@@ -112,7 +113,7 @@ __global__ void __launch_bounds__(kRopeThreads) rope_kv_store_kernel(
 
 extern "C" int bsgl_rope_kv_store(const void* qkv, int64_t qkv_row_stride, const int64_t* positions,
                                   const float* inv_freq, const int32_t* loc, void* k_slab, void* v_slab,
-                                  void* q_out, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim,
+                                  int64_t n_slots, void* q_out, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim,
                                   int dtype, void* stream) {
   using namespace bsgl;
   BSGL_REQUIRE(n_tokens >= 0, "bsgl_rope_kv_store: negative token count");
@@ -121,6 +122,7 @@ extern "C" int bsgl_rope_kv_store(const void* qkv, int64_t qkv_row_stride, const
   BSGL_REQUIRE((k_slab == nullptr) == (v_slab == nullptr) && (k_slab == nullptr) == (loc == nullptr),
                "bsgl_rope_kv_store: k_slab, v_slab and loc must be all set (store) or all NULL (rotate only)");
   BSGL_REQUIRE(n_q_heads > 0 && n_kv_heads > 0, "bsgl_rope_kv_store: bad head counts");
+  BSGL_REQUIRE(loc == nullptr || n_slots > 0, "bsgl_rope_kv_store: n_slots must be the slab's row count (S + 1)");
   BSGL_REQUIRE(head_dim > 0 && head_dim % 16 == 0 && head_dim <= 1024,
                "bsgl_rope_kv_store: head_dim must be a multiple of 16 (two 16-byte half-row chunks)");
   BSGL_REQUIRE(dtype == BSGL_BF16 || dtype == BSGL_F16, "bsgl_rope_kv_store: dtype must be bf16 or fp16");
@@ -133,10 +135,10 @@ extern "C" int bsgl_rope_kv_store(const void* qkv, int64_t qkv_row_stride, const
   if (dtype == BSGL_BF16) {
     rope_kv_store_kernel<__nv_bfloat16><<<(unsigned)n_tokens, kRopeThreads, smem, s>>>(
         (const __nv_bfloat16*)qkv, qkv_row_stride, positions, inv_freq, loc, (__nv_bfloat16*)k_slab,
-        (__nv_bfloat16*)v_slab, (__nv_bfloat16*)q_out, n_q_heads, n_kv_heads, head_dim);
+        (__nv_bfloat16*)v_slab, n_slots, (__nv_bfloat16*)q_out, n_q_heads, n_kv_heads, head_dim);
   } else {
     rope_kv_store_kernel<__half><<<(unsigned)n_tokens, kRopeThreads, smem, s>>>(
-        (const __half*)qkv, qkv_row_stride, positions, inv_freq, loc, (__half*)k_slab, (__half*)v_slab,
+        (const __half*)qkv, qkv_row_stride, positions, inv_freq, loc, (__half*)k_slab, (__half*)v_slab, n_slots,
         (__half*)q_out, n_q_heads, n_kv_heads, head_dim);
   }
   return check_launch("rope_kv_store_kernel");

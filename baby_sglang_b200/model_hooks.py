@@ -47,10 +47,27 @@ def _inv_freq_f32(rotary: torch.nn.Module) -> torch.Tensor:
     return cached[1]
 
 
+def _module_global(obj, method: str, name: str, module: str):
+    """The object `name` as the module that defines `type(obj).method` sees it (e.g. the `SimpleAttentionBackend`
+    qwen2.py imported at :7, the `SimplifiedForwardBatch` scheduler.py imported at :8) -- the exact class the
+    unchanged caller uses, whatever `sys.modules` holds by now.  Falls back to importing `module` by name."""
+    fn = getattr(type(obj), method, None)
+    found = getattr(fn, "__globals__", {}).get(name) if fn is not None else None
+    if found is None:
+        import importlib
+        found = getattr(importlib.import_module(module), name)
+    return found
+
+
 def _fused_attention_forward(self, positions: torch.Tensor, hidden_states: torch.Tensor, forward_batch):
     """Drop-in for Qwen2Attention.forward (qwen2.py:179-197) with K5 in place of split + RoPE + store."""
-    import attn_backend   # the drop-in module (first on sys.path wherever the reference stack runs)
-
+    backend = self.__dict__.get("_bsgl_backend")
+    if backend is None:
+        backend = _module_global(self.attn, "forward", "SimpleAttentionBackend", "attn_backend")
+        if not hasattr(backend, "forward_decode"):
+            raise RuntimeError("install_fused_rope_kv_store needs the drop-in attn_backend (the model was built on "
+                               "the reference's own backend)")
+        self.__dict__["_bsgl_backend"] = backend
     qkv = self.qkv_proj.qkv_proj(hidden_states)                      # the fused Linear (qwen2.py:283)
     pool = forward_batch.token_to_kv_pool
     layer_id = self.attn.layer_id
@@ -61,7 +78,7 @@ def _fused_attention_forward(self, positions: torch.Tensor, hidden_states: torch
         raise RuntimeError(f"fused RoPE store needs activation dtype {qkv.dtype} == KV pool dtype {k_slab.dtype}")
     q = ops.rope_kv_store(qkv, positions, _inv_freq_f32(self.rotary_emb), self.num_heads, self.num_kv_heads,
                           self.head_dim, k_slab, v_slab, forward_batch.out_cache_loc)
-    attn_output = attn_backend.SimpleAttentionBackend.forward(q, None, None, self.attn, forward_batch, False)
+    attn_output = backend.forward(q, None, None, self.attn, forward_batch, False)
     return self.o_proj(attn_output)
 
 
@@ -117,7 +134,10 @@ def _batched_sample_next_ids(self, logits: torch.Tensor, batch_requests, mode: s
                             dtype=torch.float32).to(dev, non_blocking=True)
     if logits.dim() != 2:
         logits = logits.reshape(-1, logits.shape[-1])
-    return ops.greedy_sample(logits, qo, prev, indptr, pens, batch=B)
+    ids = ops.greedy_sample(logits, qo, prev, indptr, pens, batch=B)
+    # `_process_results` reads every id with `.item()` (scheduler.py:553): hand it a host tensor so that is ONE
+    # device->host copy per step instead of B blocking ones
+    return ids.cpu()
 
 
 def install_batched_greedy_sampler(scheduler) -> None:
@@ -136,7 +156,7 @@ def _device_prepare_prefill_batch(self, batch_requests):
     new slots | 0 ...] over all C cells), but: one H2D copy of a packed [5, B] descriptor instead of three
     `torch.tensor` uploads, one K7 launch instead of `zeros([B, C])` + two slice writes per request + a
     whole-row index-put, and no `.item()` (the reference syncs once per request at :439)."""
-    import forward_batch as fb_mod   # the drop-in module (first on sys.path wherever the reference stack runs)
+    fb_cls = _module_global(self, "_prepare_prefill_batch", "SimplifiedForwardBatch", "forward_batch")
 
     B = len(batch_requests)
     rows = self.req_to_token_pool.alloc(B)
@@ -180,7 +200,7 @@ def _device_prepare_prefill_batch(self, batch_requests):
         req.req_pool_idx = int(row)
         req.seq_len = s
 
-    return fb_mod.SimplifiedForwardBatch.create_prefill_batch(
+    return fb_cls.create_prefill_batch(
         input_ids=concat_input_ids, req_pool_indices=desc[0], seq_lens=desc[2], out_cache_loc=out_cache_loc,
         req_to_token_pool=pool, token_to_kv_pool=self.token_to_kv_pool, prefix_lens=desc[1])
 
@@ -188,7 +208,7 @@ def _device_prepare_prefill_batch(self, batch_requests):
 def _device_prepare_decode_batch(self, batch_requests):
     """Drop-in for Scheduler._prepare_decode_batch (scheduler.py:454-507): the B scalar device writes
     `req_to_token[r, seq_len] = slot` (:486-488) become one K7 launch and the three uploads one."""
-    import forward_batch as fb_mod
+    fb_cls = _module_global(self, "_prepare_decode_batch", "SimplifiedForwardBatch", "forward_batch")
 
     B = len(batch_requests)
     new_kv_slots = self.token_to_kv_pool.alloc(B)
@@ -214,7 +234,7 @@ def _device_prepare_decode_batch(self, batch_requests):
     packed = torch.tensor([rows, lens, ids], dtype=torch.int64).to(self.device, non_blocking=True)
     pool = self.req_to_token_pool
     ops.page_table_append(pool.req_to_token, packed[0], packed[1], new_kv_slots)
-    return fb_mod.SimplifiedForwardBatch.create_decode_batch(
+    return fb_cls.create_decode_batch(
         input_ids=packed[2], req_pool_indices=packed[0], seq_lens=packed[1], out_cache_loc=new_kv_slots,
         req_to_token_pool=pool, token_to_kv_pool=self.token_to_kv_pool)
 

@@ -99,7 +99,7 @@ def kv_store(k_slab: torch.Tensor, v_slab: torch.Tensor, loc: torch.Tensor,
     if not _ok(cache_v):
         cache_v = cache_v.contiguous()
     lib = _lib.load()
-    rc = lib.bsgl_kv_store(k_slab.data_ptr(), v_slab.data_ptr(), loc.data_ptr(), cache_k.data_ptr(),
+    rc = lib.bsgl_kv_store(k_slab.data_ptr(), v_slab.data_ptr(), S1, loc.data_ptr(), cache_k.data_ptr(),
                            cache_v.data_ptr(), T, H, D, cache_k.stride(0), cache_k.stride(1),
                            cache_v.stride(0), cache_v.stride(1), dtype_code(cache_k.dtype),
                            dtype_code(k_slab.dtype), _stream())
@@ -150,7 +150,7 @@ def rope_kv_store(qkv: torch.Tensor, positions: torch.Tensor, inv_freq: torch.Te
     rc = _lib.load().bsgl_rope_kv_store(
         qkv.data_ptr(), qkv.stride(0), positions.data_ptr(), inv_freq.data_ptr(),
         loc.data_ptr() if store else null, k_slab.data_ptr() if store else null,
-        v_slab.data_ptr() if store else null, q_out.data_ptr(), T, Hq, Hkv, D, dtype_code(qkv.dtype), _stream())
+        v_slab.data_ptr() if store else null, int(k_slab.shape[0]) if store else 0, q_out.data_ptr(), T, Hq, Hkv, D, dtype_code(qkv.dtype), _stream())
     _lib.check(rc, "bsgl_rope_kv_store")
     _count()
     return q_out

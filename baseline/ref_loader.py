@@ -1,4 +1,7 @@
-"""TEST INFRASTRUCTURE ONLY — load the UNMODIFIED reference (baby-llm/baby-sglang) in isolation.
+"""Load the UNMODIFIED reference (baby-llm/baby-sglang) in isolation — harness code, not product: the package
+`baby_sglang_b200/` never imports it.  Consumers: tests/ (reference stack vs drop-in stack), tests/golden/make_*.py
+(fixture generation), bench.py (the reference's own scheduler + model DRIVING the drop-in path for the end-to-end
+decode tok/s number, and the reference's CPU path as the timed baseline).
 
 The reference is a flat directory of modules that import each other by bare top-level
 name (`from attn_backend import ...`, qwen2.py:5-7, scheduler.py:8-9), so "which
@@ -7,9 +10,9 @@ mechanism.  `load_stack()` imports the reference's modules with an optional shad
 directory in front (our drop-in modules), then removes them from `sys.modules` again so
 two stacks (reference-only, and reference + drop-in) can live in one process.
 
-Reference location: $BABYSGL_REF, else /root/reference, else <repo>/baseline/_ref.
-None of these exists on the GPU box unless a checkout was staged by hand; callers must
-skip when `find_reference()` returns None.
+Reference location: $BABYSGL_REF, else /root/reference, else <repo>/baseline/_ref.  The last one is
+staged by `scripts/stage_reference.py` (git-ignored, not gpurun-ignored, so it travels to the GPU box with
+the snapshot, like the built .so); callers must skip when `find_reference()` returns None.
 """
 from __future__ import annotations
 

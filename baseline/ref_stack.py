@@ -1,0 +1,198 @@
+"""Harness code (not product): build and run the reference's UNCHANGED scheduler / radix cache / overlap worker /
+qwen2 model, either pure (every module the reference's own) or with the four drop-in modules shadowing
+`attn_backend`, `forward_batch`, `memory_pool`, `tp_runtime` (the plug mechanism, qwen2.py:5-7, scheduler.py:8-9).
+
+Used by tests/test_reference_stack.py (pure stack vs drop-in stack on the same GPU) and by bench.py (the
+unchanged scheduler driving the drop-in path for the end-to-end decode tok/s number).
+
+The recorder below only LISTENS: it wraps `sample_next_ids` where the reference's scheduler / overlap worker look
+it up (scheduler.py:11, overlap_worker.py:10) and notes the top-2 logits of every sampled token, so that a
+differing greedy token can be classified as a numerical tie or a real mismatch.  It never changes a result.
+"""
+from __future__ import annotations
+
+import math
+import os
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from . import ref_loader
+
+
+def deterministic_weights(model: torch.nn.Module, scale: float = 1.0) -> None:
+    """Same recipe as tests/harness_model.py: every parameter from a generator seeded by crc32(name)."""
+    import zlib
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            g = torch.Generator().manual_seed(zlib.crc32(name.encode()))
+            r = torch.randn(p.shape, generator=g, dtype=torch.float32)
+            if name.endswith("norm.weight") or "layernorm" in name:
+                val = 1.0 + 0.1 * r
+            elif name.endswith(".bias"):
+                val = 0.1 * r
+            elif "embed_tokens" in name:
+                val = r
+            else:
+                val = r * (scale / (p.shape[-1] ** 0.5))
+            p.copy_(val.to(p.dtype))
+
+
+def bf16_ulp(x: float) -> float:
+    """Spacing of bf16 numbers at |x| (8 significant bits)."""
+    return 2.0 ** (math.floor(math.log2(max(abs(x), 2.0 ** -126))) - 7)
+
+
+@dataclass
+class SampleLog:
+    """top-1 / top-2 logit of every sampled token, in call order."""
+    top2: List[torch.Tensor] = field(default_factory=list)      # each [2] float32 on the device
+
+    def values(self) -> List[List[float]]:
+        if not self.top2:
+            return []
+        return torch.stack(self.top2).cpu().tolist()
+
+
+def _listen(stack, log: SampleLog) -> None:
+    for mod in (stack.scheduler, stack.overlap_worker):
+        if mod is None or not hasattr(mod, "sample_next_ids"):
+            continue
+        inner = mod.sample_next_ids
+
+        def recorder(logits, *a, _inner=inner, **kw):
+            log.top2.append(torch.topk(logits.reshape(-1).float(), 2).values)
+            return _inner(logits, *a, **kw)
+
+        mod.sample_next_ids = recorder
+
+
+class StepTracker:
+    """Maps the recorder's call-order log onto (request, step).  Both `_process_results` (scheduler.py:548-589) and
+    `_process_results_overlap` (:700-761) commit batches in the order they were sampled, one `sample_next_ids`
+    call per request of the batch; a request's output list grows by one exactly when its sample was kept (overlap
+    mode drops the extra step of an already finished request, :741-747)."""
+
+    def __init__(self, scheduler, log: SampleLog):
+        self.log, self.kept = log, []            # kept: (record index, prompt key) per committed token
+        self._cursor = 0
+        cls = type(scheduler)
+
+        def wrap(name, get_reqs):
+            inner = getattr(cls, name)
+
+            def method(this, *a, **kw):
+                reqs = get_reqs(*a, **kw)
+                before = [len(r.output_ids) for r in reqs]
+                out = inner(this, *a, **kw)
+                for i, (r, n0) in enumerate(zip(reqs, before)):
+                    if len(r.output_ids) > n0:
+                        self.kept.append((self._cursor + i, tuple(r.input_ids.tolist())))
+                self._cursor += len(reqs)
+                return out
+            setattr(scheduler, name, method.__get__(scheduler, cls))
+
+        wrap("_process_results", lambda next_ids, batch_requests, mode: batch_requests)
+        wrap("_process_results_overlap", lambda batch, next_ids_cpu: batch.batch_requests)
+
+    def start_run(self) -> None:
+        self.kept, self._cursor, self.log.top2 = [], 0, []
+
+    def margins(self, prompts: Sequence[torch.Tensor]) -> List[List[List[float]]]:
+        """[request][step] = [top1, top2] of the logits the kept token was sampled from."""
+        vals = self.log.values()
+        index = {tuple(p.tolist()): i for i, p in enumerate(prompts)}
+        out: List[List[List[float]]] = [[] for _ in prompts]
+        for rec, key in self.kept:
+            out[index[key]].append(vals[rec])
+        return out
+
+
+@dataclass
+class StackRun:
+    stack: object
+    scheduler: object
+    model: object
+    log: SampleLog
+    tracker: Optional[StepTracker] = None
+
+    def state(self) -> Dict[str, object]:
+        """The index state the north star requires to be bit-exact."""
+        s = self.scheduler
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        return {"req_to_token": s.req_to_token_pool.req_to_token.clone().cpu(),
+                "free_slots": s.token_to_kv_pool.free_slots.clone().cpu().to(torch.int32),
+                "free_rows": list(s.req_to_token_pool.free_slots),
+                "evictable_size": int(s.tree_cache.evictable_size_),
+                "kv_available": int(s.token_to_kv_pool.available_size())}
+
+
+def build(shadow_dir: Optional[str], cfg_kwargs: dict, device: str, dtype: torch.dtype, max_total_tokens: int,
+          max_requests: int, hooks: Sequence[str] = (), listen: bool = True, init: str = "deterministic") -> StackRun:
+    """Reference scheduler + model on `device`; `shadow_dir=None` is the pure reference, `DROPIN_DIR` the product.
+    `hooks` ⊆ {"rope", "sampler", "prep", "graph"} installs the row-(f) kernels (baby_sglang_b200.model_hooks) on
+    the instances."""
+    st = ref_loader.load_stack(shadow_dir=shadow_dir)
+    os.environ["BABYSGL_MAX_TOTAL_TOKENS"] = str(max_total_tokens)     # scheduler.py:33-36
+    os.environ["BABYSGL_MAX_REQUESTS"] = str(max_requests)
+    cfg = st.model_loader.BabyQwenConfig(**cfg_kwargs)
+    if init == "deterministic":
+        model = st.qwen2.BabyQwen2ForCausalLM(cfg).float().eval()
+        deterministic_weights(model)
+        model = model.to(device=device, dtype=dtype)
+    else:   # big geometries: construct on the device, default torch init, seeded
+        torch.manual_seed(0)
+        prev = torch.get_default_dtype()
+        torch.set_default_dtype(dtype)
+        try:
+            with torch.device(device):
+                model = st.qwen2.BabyQwen2ForCausalLM(cfg).eval()
+        finally:
+            torch.set_default_dtype(prev)
+        for m in model.modules():       # rotary buffers are built with explicit CPU/float math in the reference
+            for name, buf in list(m.named_buffers(recurse=False)):
+                setattr(m, name, buf.to(device))
+    sched = st.scheduler.Scheduler(model, tokenizer=None)
+    log = SampleLog()
+    tracker = None
+    if listen:
+        _listen(st, log)
+        tracker = StepTracker(sched, log)
+    if hooks:
+        from baby_sglang_b200 import model_hooks
+        if "rope" in hooks:
+            model_hooks.install_fused_rope_kv_store(model)
+        if "sampler" in hooks:
+            model_hooks.install_batched_greedy_sampler(sched)
+        if "prep" in hooks:
+            model_hooks.install_device_batch_prep(sched)
+        if "graph" in hooks:
+            model_hooks.install_cuda_graph_decode(model)
+    return StackRun(st, sched, model, log, tracker)
+
+
+def classify_divergence(ref_ids: List[List[int]], got_ids: List[List[int]], ref_margins: List[List[List[float]]],
+                        ulps: float = 2.0) -> dict:
+    """Free-running comparison of two greedy runs.  For every request: identical up to (excluding) the first
+    differing step; that step is a TIE if the reference side's own top-1/top-2 margin there is within `ulps` bf16
+    ulps of the top-1 logit (the argmax is then decided by rounding noise in either stack),
+    otherwise a MISMATCH.  `ref_margins[r][s] = [top1, top2]`."""
+    ties, bad, compared = [], [], 0
+    for r, (a, b) in enumerate(zip(ref_ids, got_ids)):
+        if len(a) != len(b):
+            bad.append({"request": r, "step": -1, "why": f"lengths {len(a)} vs {len(b)}"})
+            continue
+        for s, (x, y) in enumerate(zip(a, b)):
+            if x == y:
+                compared += 1
+                continue
+            t1, t2 = ref_margins[r][s]
+            tol = ulps * bf16_ulp(max(abs(t1), 1.0))
+            rec = {"request": r, "step": s, "ref_id": x, "got_id": y, "ref_top1": t1, "ref_margin": t1 - t2,
+                   "tie_tolerance": tol}
+            (ties if (t1 - t2) <= tol else bad).append(rec)
+            break
+    total = sum(len(a) for a in ref_ids)
+    return {"steps_total": total, "steps_compared_equal": compared, "ties": ties, "mismatches": bad}

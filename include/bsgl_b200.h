@@ -73,8 +73,10 @@ int bsgl_heads_per_group(int n_kv_heads);
 /* K1.  slab[loc[t], h, :] = src[t, h, :] for K and V in one launch.  Source rows may be
  * strided views (the reference hands `v` as a view of the fused QKV output, qwen2.py:285-290):
  * strides are in ELEMENTS; the innermost dimension must be contiguous.  src_dtype may differ
- * from slab_dtype (round-to-nearest-even cast, memory_pool.py:163-165).  Bit-exact. */
-int bsgl_kv_store(void* k_slab, void* v_slab, const int32_t* loc,
+ * from slab_dtype (round-to-nearest-even cast, memory_pool.py:163-165).  Bit-exact.
+ * n_slots = rows of each slab (S + 1): a loc[t] outside [0, n_slots) traps the kernel, like the
+ * device-side assert of the reference's index-put, instead of writing into a neighbouring layer. */
+int bsgl_kv_store(void* k_slab, void* v_slab, int64_t n_slots, const int32_t* loc,
                   const void* k_src, const void* v_src,
                   int64_t n_tokens, int n_kv_heads, int head_dim,
                   int64_t k_row_stride, int64_t k_head_stride,
@@ -167,11 +169,12 @@ int bsgl_extend_attention(const void* q, const void* k_slab, const void* v_slab,
  *   positions int64 [T], inv_freq float32 [D/2] (the module's own buffer, qwen2.py:244-245)
  *   q_out     [T, Hq, D] contiguous, rotated
  *   k_slab/v_slab[loc[t]] receive the rotated K row and the V row; all three NULL = rotate q only.
+ *   n_slots   rows of each slab (S + 1); an out-of-range loc[t] traps (see bsgl_kv_store).
  * Rounding follows the reference: cos/sin rounded to the activation dtype, every product and sum
  * rounded to it (bit-exact against the reference run on the same device). */
 int bsgl_rope_kv_store(const void* qkv, int64_t qkv_row_stride, const int64_t* positions,
                        const float* inv_freq, const int32_t* loc, void* k_slab, void* v_slab,
-                       void* q_out, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim,
+                       int64_t n_slots, void* q_out, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim,
                        int dtype, void* stream);
 
 /* K6 (the step immediately after the path).  Batched greedy sampling on the

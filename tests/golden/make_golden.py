@@ -1,5 +1,5 @@
 """Generate the golden fixtures in this directory by running the UNMODIFIED reference
-(/root/reference, imported through oracle/ref_loader.py) on seeded synthetic inputs.
+(/root/reference, imported through baseline/ref_loader.py) on seeded synthetic inputs.
 
     python tests/golden/make_golden.py            # rewrites tests/golden/*.npz
 
@@ -21,7 +21,7 @@ import torch
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 
-from oracle import ref_loader  # noqa: E402
+from baseline import ref_loader  # noqa: E402
 
 
 def bf16_bits(x: torch.Tensor) -> np.ndarray:

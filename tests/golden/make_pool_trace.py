@@ -13,7 +13,7 @@ import torch
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
-from oracle import ref_loader  # noqa: E402
+from baseline import ref_loader  # noqa: E402
 
 
 def trace(ref, seed, size, n_ops):

@@ -1,5 +1,5 @@
 """Generate tests/golden/rope_*.npz by running the UNMODIFIED reference's RotaryEmbedding
-(qwen2.py:227-268, imported through oracle/ref_loader.py) on seeded inputs, in the 16-bit
+(qwen2.py:227-268, imported through baseline/ref_loader.py) on seeded inputs, in the 16-bit
 activation dtypes the CUDA path supports.  Build container only; the .npz files are committed.
 
     python tests/golden/make_rope_golden.py
@@ -15,7 +15,7 @@ import torch
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 
-from oracle import ref_loader  # noqa: E402
+from baseline import ref_loader  # noqa: E402
 
 
 def bits16(x: torch.Tensor) -> np.ndarray:

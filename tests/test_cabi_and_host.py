@@ -47,9 +47,9 @@ def test_invalid_arguments_report_errors(lib):
     rc = lib.bsgl_partial_sizes(148, 28, 5, 128, None, None)
     assert rc == 1
     assert b"n_q_heads" in lib.bsgl_last_error()
-    rc = lib.bsgl_kv_store(None, None, None, None, None, 4, 2, 128, 256, 128, 256, 128, 0, 0, None)
+    rc = lib.bsgl_kv_store(None, None, 9, None, None, None, 4, 2, 128, 256, 128, 256, 128, 0, 0, None)
     assert rc == 1 and b"null" in lib.bsgl_last_error()
-    rc = lib.bsgl_kv_store(None, None, None, None, None, 0, 2, 128, 256, 128, 256, 128, 0, 0, None)
+    rc = lib.bsgl_kv_store(None, None, 9, None, None, None, 0, 2, 128, 256, 128, 256, 128, 0, 0, None)
     assert rc == 0   # empty store is a no-op
 
 
