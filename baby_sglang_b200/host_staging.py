@@ -72,6 +72,7 @@ class HostStagedAttention:
         stage = self._staging(qkv_host[0])
         up = [torch.cuda.Event() for _ in range(L)]
         done = [torch.cuda.Event() for _ in range(L)]
+        copied = [torch.cuda.Event() for _ in range(L)]
         self.h2d.wait_stream(cur)          # staging buffers may still be read by earlier work
         with torch.cuda.stream(self.h2d):
             stage[0].copy_(qkv_host[0], non_blocking=True)
@@ -88,6 +89,11 @@ class HostStagedAttention:
             q, k, v = self._split(stage[l % 2])
             out = self._backend.forward(q, k, v, layers[l], forward_batch, True)
             if after is not None:
+                # `after` may hand back a view of a buffer it reuses two calls later (K8's output buffers
+                # alternate with the call parity): layer l-2's download must have left it before layer l's call
+                # can overwrite it -- on this rank by a peer's stores too, which follow the peer's own call
+                if l >= 2:
+                    cur.wait_event(copied[l - 2])
                 out = after(out)
             done[l].record(cur)
             out.record_stream(self.d2h)
@@ -95,5 +101,6 @@ class HostStagedAttention:
             with torch.cuda.stream(self.d2h):
                 self.d2h.wait_event(done[l])
                 out_host[l].copy_(out, non_blocking=True)
+                copied[l].record(self.d2h)
         cur.wait_stream(self.d2h)
         cur.synchronize()                  # the caller reads out_host next

@@ -252,3 +252,92 @@ def install_device_batch_prep(scheduler) -> None:
 def uninstall_device_batch_prep(scheduler) -> None:
     for name in ("_prepare_prefill_batch", "_prepare_decode_batch"):
         scheduler.__dict__.pop(name, None)
+
+
+# ------------------------------------------------------------------------------------------------------
+# the whole decode step as one CUDA graph (small batches are launch-bound: ~37 us of host time per layer)
+# ------------------------------------------------------------------------------------------------------
+class _GraphedDecode:
+    """One captured decode forward per batch size: K4 metadata + every layer (projections, RoPE / K5, K1, K2,
+    K2c, MLP) + the LM head, replayed with in-place updates of five small input buffers.  Nothing in the step
+    takes a size from the host (the page table and the KV slabs are read in place, K4 builds the plan on the
+    device), so a replay after the batch moved on computes exactly what eager launches would."""
+
+    def __init__(self, model: torch.nn.Module, max_graphs: int = 8):
+        self.model = model
+        self.eager_forward = model.forward            # the bound class-level forward
+        self.max_graphs = max_graphs
+        self.graphs = {}                              # (B, pools) -> captured state
+        self.fb_cls = None
+        self.replays = 0
+        self.captures = 0
+
+    def _capture(self, B: int, fb):
+        dev = fb.input_ids.device
+        i64 = dict(dtype=torch.int64, device=dev)
+        st = {"ids": torch.zeros(B, **i64), "rpi": torch.zeros(B, **i64), "seq": torch.ones(B, **i64),
+              "loc": torch.zeros(B, dtype=torch.int32, device=dev)}
+        self._load(st, fb)
+        fb_cls = type(fb)
+
+        def step():
+            sfb = fb_cls.create_decode_batch(input_ids=st["ids"], req_pool_indices=st["rpi"], seq_lens=st["seq"],
+                                             out_cache_loc=st["loc"], req_to_token_pool=fb.req_to_token_pool,
+                                             token_to_kv_pool=fb.token_to_kv_pool)
+            return self.eager_forward(sfb.input_ids, sfb.positions, sfb), sfb
+
+        # eager warm-up on a side stream (lazy library initialisation must not happen under capture); it also
+        # performs this step's KV stores, which the captured replay below then repeats with identical values
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            step()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            logits, sfb = step()
+        st["graph"], st["logits"], st["fb"] = g, logits, sfb
+        self.captures += 1
+        return st
+
+    @staticmethod
+    def _load(st, fb) -> None:
+        st["ids"].copy_(fb.input_ids, non_blocking=True)
+        st["rpi"].copy_(fb.req_pool_indices, non_blocking=True)
+        st["seq"].copy_(fb.seq_lens, non_blocking=True)
+        st["loc"].copy_(fb.out_cache_loc, non_blocking=True)
+
+    def __call__(self, input_ids, positions, forward_batch, input_embeds=None):
+        if input_embeds is not None or getattr(forward_batch, "is_prefill", True) or \
+                not hasattr(type(forward_batch), "create_decode_batch") or not input_ids.is_cuda or \
+                torch.cuda.is_current_stream_capturing():
+            return self.eager_forward(input_ids, positions, forward_batch, input_embeds)
+        B = int(input_ids.shape[0])
+        key = (B, id(forward_batch.req_to_token_pool), id(forward_batch.token_to_kv_pool))
+        st = self.graphs.get(key)
+        if st is None:
+            if len(self.graphs) >= self.max_graphs:
+                self.graphs.pop(next(iter(self.graphs)))
+            st = self.graphs[key] = self._capture(B, forward_batch)
+        else:
+            self._load(st, forward_batch)
+        st["graph"].replay()
+        self.replays += 1
+        return st["logits"]
+
+
+def install_cuda_graph_decode(model: torch.nn.Module, max_graphs: int = 8) -> "_GraphedDecode":
+    """Replay the decode forward of `model` (the reference's unchanged BabyQwen2ForCausalLM on the drop-in
+    backend) as one CUDA graph per batch size, captured on first use; prefill batches run eagerly.  The returned
+    logits are a static buffer: valid until the next decode forward of the same batch size (the reference's
+    scheduler and overlap worker sample from them at once, scheduler.py:154-160, overlap_worker.py:123-150).
+    Install after the other hooks (K5 is captured inside the graph)."""
+    hook = _GraphedDecode(model, max_graphs)
+    model.forward = hook
+    model.__dict__["_bsgl_graphed_decode"] = hook
+    return hook
+
+
+def uninstall_cuda_graph_decode(model: torch.nn.Module) -> None:
+    model.__dict__.pop("forward", None)
+    model.__dict__.pop("_bsgl_graphed_decode", None)

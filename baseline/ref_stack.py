@@ -109,6 +109,60 @@ class StepTracker:
         return out
 
 
+class Forcer:
+    """Teacher forcing for `Scheduler.run_batch`: the stack's own `_sample_next_ids` (the reference's method, or the
+    K6 hook) runs and its ids are RECORDED, but the ids handed back to the scheduler are the given ones, so the run
+    follows another run's trajectory exactly.  With it the index state (page table, slot FIFO, radix tree sizes)
+    of two stacks must agree bit for bit even where a bf16 tie would let their free-running tokens part, and every
+    one of the 64 steps of every request gets compared, not only those before a first departure."""
+
+    def __init__(self, scheduler):
+        self.scheduler = scheduler
+        self.inner = scheduler._sample_next_ids          # bound: class method or an installed hook
+        self.want: Optional[List[List[int]]] = None
+        self.index: Dict[tuple, int] = {}
+        self.own: List[List[int]] = []
+        scheduler._sample_next_ids = self._call
+
+    def start_run(self, prompts: Sequence[torch.Tensor], want_ids: List[List[int]]) -> None:
+        self.want = want_ids
+        self.index = {tuple(p.tolist()): i for i, p in enumerate(prompts)}
+        self.own = [[] for _ in prompts]
+
+    def _call(self, logits, batch_requests, mode):
+        own = self.inner(logits, batch_requests, mode)
+        if self.want is None:
+            return own
+        own_list = [int(x) for x in own.tolist()]
+        forced = []
+        for req, o in zip(batch_requests, own_list):
+            r = self.index[tuple(req.input_ids.tolist())]
+            self.own[r].append(o)
+            forced.append(self.want[r][len(req.output_ids)])
+        return torch.tensor(forced, dtype=own.dtype, device=own.device)
+
+
+def classify_forced(ref_ids: List[List[int]], own_ids: List[List[int]], ref_margins: List[List[List[float]]],
+                    ulps: float = 2.0) -> dict:
+    """Teacher-forced comparison: EVERY step of every request.  A differing own argmax is a TIE if the reference
+    side's top-1/top-2 margin at that step is within `ulps` bf16 ulps, else a MISMATCH."""
+    ties, bad, equal = [], [], 0
+    for r, (a, b) in enumerate(zip(ref_ids, own_ids)):
+        if len(a) != len(b):
+            bad.append({"request": r, "step": -1, "why": f"lengths {len(a)} vs {len(b)}"})
+            continue
+        for s, (x, y) in enumerate(zip(a, b)):
+            if x == y:
+                equal += 1
+                continue
+            t1, t2 = ref_margins[r][s]
+            tol = ulps * bf16_ulp(max(abs(t1), 1.0))
+            rec = {"request": r, "step": s, "ref_id": x, "got_id": y, "ref_top1": t1, "ref_margin": t1 - t2,
+                   "tie_tolerance": tol}
+            (ties if (t1 - t2) <= tol else bad).append(rec)
+    return {"steps_total": sum(len(a) for a in ref_ids), "steps_equal": equal, "ties": ties, "mismatches": bad}
+
+
 @dataclass
 class StackRun:
     stack: object
@@ -196,3 +250,76 @@ def classify_divergence(ref_ids: List[List[int]], got_ids: List[List[int]], ref_
             break
     total = sum(len(a) for a in ref_ids)
     return {"steps_total": total, "steps_compared_equal": compared, "ties": ties, "mismatches": bad}
+
+
+# ------------------------------------------------------------------------------------------------------
+# end-to-end decode step timing through the unchanged scheduler (bench.py: the "& decode tok/s" half of the metric)
+# ------------------------------------------------------------------------------------------------------
+def seed_decode_state(run: StackRun, batch: int, ctx: int, max_new_tokens: int, seed: int = 0,
+                      chunk: int = 32) -> None:
+    """Put `batch` requests with `ctx`-token contexts straight into the scheduler's decode phase.
+
+    The reference cannot prefill this state itself at BASELINE size: its prefill computes LM-head logits for EVERY
+    prompt token (qwen2.py:31-36) -- 256 x 4096 tokens x 152 064 vocab = 319 GB of bf16.  So the page-table rows and
+    KV slots are allocated by the scheduler's own `_prepare_prefill_batch` (scheduler.py:381-452: row FIFO, slot
+    FIFO, page-table rows written exactly as a real prefill would), the model forward of the prefill is skipped and
+    the KV slabs are filled with N(0,1) instead; every request then holds one (arbitrary) first output token and
+    sits in `decoding_batch`, as after `_process_results(..., "prefill")` (:566-579) without the radix insertion.
+    From here on the scheduler's normal loop body runs unchanged."""
+    sched, st = run.scheduler, run.stack
+    dev = sched.device
+    g = torch.Generator().manual_seed(seed)
+    vocab = run.model.config.vocab_size
+    sched.waiting_queue.clear()
+    sched.decoding_batch.clear()
+    sched.finished_requests.clear()
+    sched.est_new_token_ratio = sched.r_init
+    reqs = []
+    for _ in range(batch):
+        ids = torch.randint(0, vocab, (ctx,), generator=g).to(dev)
+        reqs.append(st.request.Request(
+            input_ids=ids, output_ids=[], max_new_tokens=max_new_tokens + 1, temperature=1.0, top_k=0, top_p=1.0,
+            do_sample=False, repetition_penalty=1.0, eos_id=-1,
+            prefix_indices=torch.tensor([], dtype=torch.int32), last_node=None, num_cached_tokens=0,
+            constraint_state=None))
+    for i in range(0, batch, chunk):
+        sched._prepare_prefill_batch(reqs[i:i + chunk])          # rows + slots + page-table rows; batch discarded
+    pool = sched.token_to_kv_pool
+    for l in range(pool.layer_num):
+        pool.k_buffer[l].normal_()
+        pool.v_buffer[l].normal_()
+    first = torch.randint(0, vocab, (batch,), generator=g).tolist()
+    for r, t in zip(reqs, first):
+        r.output_ids.append(int(t))
+        sched.decoding_batch.append(r)
+    torch.cuda.synchronize()
+
+
+def timed_decode_steps(run: StackRun, steps: int, warmup: int = 2) -> dict:
+    """`steps` iterations of the body of `Scheduler.run_batch`'s loop (scheduler.py:137-163, steps 2-6), each
+    timed on the host across a device synchronise (the step ends in `.item()` reads anyway) and on the device with
+    CUDA events.  Returns per-step times and the ids sampled at every step."""
+    import time
+    sched, model = run.scheduler, run.model
+    host_ms, dev_ms, ids = [], [], []
+    for it in range(warmup + steps):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        running_batch, mode = sched._select_batch_to_run()
+        if mode != "decode":
+            raise RuntimeError(f"expected a decode step, scheduler chose {mode!r}")
+        fb = sched._prepare_forward(running_batch, mode)
+        with torch.no_grad():
+            logits = model(fb.input_ids, fb.positions, fb)
+        next_ids = sched._sample_next_ids(logits, running_batch, mode)
+        sched._process_results(next_ids, running_batch, mode)
+        e1.record()
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        if it >= warmup:
+            host_ms.append((t1 - t0) * 1e3)
+            dev_ms.append(e0.elapsed_time(e1))
+        ids.append([int(r.output_ids[-1]) for r in running_batch])
+    return {"host_ms": host_ms, "dev_ms": dev_ms, "ids": ids, "batch": len(sched.decoding_batch)}

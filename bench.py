@@ -6,22 +6,30 @@
 Workload `ns` (default; BASELINE.json north star): Qwen2.5-7B attention geometry (28 q / 4 kv heads,
 D=128, 28 layers), paged decode, batch 256, context 4096, page size 1, bf16, fragmented page table.
 One STEP = one decode step of the hot path: the K4 metadata build (once) and, for each of the 28
-layers, K1 kv_store of the new token + K2 paged split-KV attention + K2c merge.
+layers, K1 kv_store of the new token + K2 paged split-KV attention + K2c merge (under KV-head TP also the
+rank's o_proj shard with the SUM all-reduce, K8).
 
-`value`  algorithmic GB/s (SURVEY.md §8d formula) with q/k/v already resident in HBM.
-`e2e`    the same step driven through the reference-facing plugin call
-         (`SimpleAttentionBackend.forward`, drop-in module) from pinned HOST buffers: per layer
-         q/k/v are copied host->device and the attention output device->host inside the timed region.
-`roofline`  the dominant kernel (paged_attention_kernel) timed alone with CUDA events.
-`cpu_baseline`  the oracle (CPU port of the reference path) on a bounded sample of the same workload.
+`value`        algorithmic GB/s (SURVEY.md §8d formula) with q/k/v already resident in HBM.
+`e2e`          the same step driven through the reference-facing plugin call (`SimpleAttentionBackend.forward`,
+               drop-in module) from pinned HOST buffers: per layer q/k/v are copied host->device and the attention
+               output device->host inside the timed region.
+`roofline`     the dominant kernel (paged_attention_kernel) timed alone with CUDA events.
+`parity_check` sampled rows of the timed configuration against the oracle (tolerance 2e-2), per workload.
+`decode_tok_per_s`  the other half of the metric: the reference's UNCHANGED scheduler + Qwen2.5-7B-geometry model
+               (random init) on the drop-in path, B=256, ctx 4096, 64 greedy decode steps; tok/s = 256 / median step.
+`sharded`      config C5 (Qwen2.5-32B, B=1024 ragged, KV-head TP = N with the o_proj all-reduce) in the same line.
+`small_kernels` K1 / K5 / K6 rooflines.
+`cpu_baseline` the reference's own modules (when a checkout is reachable, kind "reference") or the oracle port on
+               the box's host cores, bounded sample.
 
-N > 1: request-batch data parallelism (independent requests per rank, no collective in the data
-path) -> "scaling": "weak".  Workload c5 (Qwen2.5-32B KV-head TP with the o_proj
-all-reduce) is the sharded-with-collective configuration.
+N > 1: the sharding is `tp_runtime.plan_parallelism`'s: KV-head tensor parallelism where Hkv % N == 0 (7B: N = 2, 4;
+32B: N <= 8) with the o_proj partial + SUM all-reduce inside the timed step ("scaling": "strong"); request-batch data
+parallelism otherwise (7B at N = 8; independent requests per rank, no collective, "scaling": "weak").
 """
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import statistics
@@ -35,10 +43,10 @@ import torch
 REPO = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, REPO)
 
-GEOMETRY = {  # name: (Hq, Hkv, D, layers, hidden)
-    "qwen2.5-1.5b": (12, 2, 128, 28, 1536),
-    "qwen2.5-7b": (28, 4, 128, 28, 3584),
-    "qwen2.5-32b": (40, 8, 128, 64, 5120),
+GEOMETRY = {  # name: (Hq, Hkv, D, layers, hidden, intermediate, vocab)
+    "qwen2.5-1.5b": (12, 2, 128, 28, 1536, 8960, 151936),
+    "qwen2.5-7b": (28, 4, 128, 28, 3584, 18944, 152064),
+    "qwen2.5-32b": (40, 8, 128, 64, 5120, 27648, 152064),
 }
 WORKLOADS = {
     # name: (model, batch, ctx_lo, ctx_hi, layers_resident)
@@ -47,33 +55,41 @@ WORKLOADS = {
     "c4": ("qwen2.5-7b", 512, 4096, 32768, 1),
     "c5": ("qwen2.5-32b", 1024, 512, 8192, 1),
 }
-METRIC = "paged decode attn HBM GB/s, Qwen2.5-7B bs=256 ctx=4K"
+METRIC = "paged decode attn HBM GB/s & decode tok/s, Qwen2.5-7B bs=256 ctx=4K"
+TOL = 2e-2
 
 
-def peaks():
+def _peaks_file():
     path = os.path.join(REPO, "MEASURED_PEAKS.json")
     if os.path.isfile(path):
         with open(path) as f:
-            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+            return json.load(f)
+    return None
+
+
+def peaks():
+    p = _peaks_file()
+    if p:
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def tensor_peak():
+    p = _peaks_file()
+    if p:
+        return float(p["bf16_tflops"]), "measured burst (MEASURED_PEAKS.json bf16_tflops)"
+    return 1590.0, "fallback (B200_PROFILING.md 1.59 PFLOP/s)"
 
 
 def traffic_from_profiles(key):
     """dram bytes per launch of the dominant kernel, from the committed ncu --set full capture (or None)."""
-    path = os.path.join(REPO, "profiles", "r1_traffic.json")
-    try:
-        with open(path) as f:
-            return int(json.load(f)[key]["dram_bytes"])
-    except Exception:
-        return None
-
-
-def tensor_peak():
-    path = os.path.join(REPO, "MEASURED_PEAKS.json")
-    if os.path.isfile(path):
-        with open(path) as f:
-            return float(json.load(f)["bf16_tflops"]), "measured burst (MEASURED_PEAKS.json bf16_tflops)"
-    return 1590.0, "fallback (B200_PROFILING.md 1.59 PFLOP/s)"
+    for name in ("r2_traffic.json", "r1_traffic.json"):
+        try:
+            with open(os.path.join(REPO, "profiles", name)) as f:
+                return int(json.load(f)[key]["dram_bytes"])
+        except Exception:
+            continue
+    return None
 
 
 def extend_flops(Hq, D, prefix, ext):
@@ -143,6 +159,11 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def _free():
+    gc.collect()
+    torch.cuda.empty_cache()
+
+
 # ------------------------------------------------------------------------------------------------
 # workload construction
 # ------------------------------------------------------------------------------------------------
@@ -158,13 +179,22 @@ class _Layer:
         self.tp_v_head_num = Hkv
 
 
+def _dropin():
+    d = os.path.join(REPO, "baby_sglang_b200", "dropin")
+    if d not in sys.path:
+        sys.path.insert(0, d)
+    import attn_backend
+    import forward_batch
+    import memory_pool
+    import tp_runtime
+    return attn_backend, forward_batch, memory_pool, tp_runtime
+
+
 def build_workload(name, device, seed, Hkv_override=None, Hq_override=None):
     """Pools (drop-in classes), fragmented page table and per-layer q/k/v for one decode step."""
-    sys.path.insert(0, os.path.join(REPO, "baby_sglang_b200", "dropin"))
-    import memory_pool  # drop-in
-
+    _, _, memory_pool, _ = _dropin()
     model, B, lo, hi, L = WORKLOADS[name]
-    Hq, Hkv, D, _, hidden = GEOMETRY[model]
+    Hq, Hkv, D, _, hidden = GEOMETRY[model][:5]
     if Hkv_override:
         Hq, Hkv = Hq_override, Hkv_override
     g = torch.Generator(device=device).manual_seed(seed)
@@ -190,18 +220,19 @@ def build_workload(name, device, seed, Hkv_override=None, Hq_override=None):
     r2t_pool.req_to_token.copy_(table)
     rpi = torch.arange(B, dtype=torch.int64, device=device)
     out_cache_loc = r2t_pool.req_to_token[rpi, seq - 1].contiguous()           # slot of the token being decoded
-    w = dict(name=name, model=model, B=B, Hq=Hq, Hkv=Hkv, D=D, L=L, hidden=hidden, seq=seq, C=C, S=S,
-             kv_pool=kv_pool, r2t_pool=r2t_pool, rpi=rpi, out_cache_loc=out_cache_loc,
-             sum_seq=int(seq.sum().item()), layers=[_Layer(l, Hq, Hkv, D) for l in range(L)])
-    return w
+    return dict(name=name, model=model, B=B, Hq=Hq, Hkv=Hkv, D=D, L=L, hidden=hidden, seq=seq, C=C, S=S,
+                kv_pool=kv_pool, r2t_pool=r2t_pool, rpi=rpi, out_cache_loc=out_cache_loc,
+                sum_seq=int(seq.sum().item()), layers=[_Layer(l, Hq, Hkv, D) for l in range(L)])
 
 
 def measure_extend_c3(device, reps=20):
     """Config C3: Qwen2.5-7B geometry, B=16, prefix_i ~ U[0,8192] (first two forced to 0 and
-    8192), 512 new tokens each, bf16, fragmented page table; K3 (tcgen05) timed alone with CUDA events.
-    The 151 MB KV working set is re-read across launches from HBM/L2 mix; the kernel is tensor-bound."""
+    8192), 512 new tokens each, bf16, fragmented page table; K3 (tcgen05) timed alone with CUDA events, then a
+    sample of its rows checked against the oracle.  The 151 MB KV working set is re-read across launches from an
+    HBM/L2 mix; the kernel is tensor-bound."""
     from baby_sglang_b200 import ops
-    Hq, Hkv, D, _, _ = GEOMETRY["qwen2.5-7b"]
+    from oracle import sampled_check as SC
+    Hq, Hkv, D = GEOMETRY["qwen2.5-7b"][:3]
     B, ext_len, max_prefix = 16, 512, 8192
     g = torch.Generator().manual_seed(0)
     prefix = torch.randint(0, max_prefix + 1, (B,), generator=g)
@@ -242,57 +273,51 @@ def measure_extend_c3(device, reps=20):
     fl = extend_flops(Hq, D, prefix.tolist(), ext.tolist())
     peak, src = tensor_peak()
     ach = fl / ms / 1e9
+    par = SC.extend_rows(q, k_slab, v_slab, r2t, rpi, seq_d, pre_d, out, SC.pick_requests(seq, 4, seed=2))
+    par.update(tol=TOL, ok=par["max_abs_err"] <= TOL)
     return {"bound": "tensor", "kernel": "extend_attention_kernel (tcgen05/TMEM)", "achieved": round(ach, 1),
             "peak": peak, "unit": "TFLOP/s", "frac": round(ach / peak, 4), "peak_source": src,
             "flops_per_launch": fl, "avg_launch_ms": round(ms, 5), "traffic": traffic_from_profiles("extend_c3"),
-            "workload": "qwen2.5-7b extend (config C3): B=16, prefix U[0,8192], 512 new tokens each, bf16"}
+            "workload": "qwen2.5-7b extend (config C3): B=16, prefix U[0,8192], 512 new tokens each, bf16",
+            "parity_check": par}
 
 
-def run_b200(args, rank, world, device):
+def measure_decode_workload(workload, rank, world, device, steps, warmup, oproj="fused", sample_clocks=False,
+                            with_e2e=True, roof_reps=None):
+    """One decode workload under the sharding `tp_runtime.plan_parallelism` picks for `world`.  Returns a dict of
+    measurements (times are the max over ranks)."""
     from baby_sglang_b200 import ops
-    model_name = WORKLOADS[args.workload][0]
+    from baby_sglang_b200.host_staging import HostStagedAttention
+    from oracle import sampled_check as SC
+    attn_backend, forward_batch, _, tp_runtime = _dropin()
+    model_name = WORKLOADS[workload][0]
     Hq_full, Hkv_full = GEOMETRY[model_name][0], GEOMETRY[model_name][1]
-    # c5: KV-head tensor parallelism (rank r owns Hkv/t KV heads of EVERY request; identical page table on all
-    # ranks; one SUM all-reduce of the o_proj partial per layer).  Everything else: request-batch DP.
-    tp = args.workload == "c5" and world > 1 and Hkv_full % world == 0
-    # K3 is timed alone and first, like the burst peak it is compared with (after the 28-layer decode loop the
-    # GPU sits at its power cap and the same kernel runs ~10 % slower).
-    extend = measure_extend_c3(device) if (world == 1 and rank == 0) else None
-    if tp:
-        w = build_workload(args.workload, device, seed=1234, Hkv_override=Hkv_full // world,
-                           Hq_override=Hq_full // world)
-    else:
-        w = build_workload(args.workload, device, seed=1234 + rank)
-    import attn_backend   # drop-in modules (sys.path set by build_workload)
-    import forward_batch
-    import tp_runtime
+    plan = tp_runtime.plan_parallelism(Hq_full, Hkv_full, world)
+    tp = plan.mode == "kv_head_tp"
+    if tp:      # rank r owns Hkv/t KV heads of EVERY request; identical page table on all ranks
+        w = build_workload(workload, device, seed=1234, Hkv_override=plan.kv_heads_per_rank,
+                           Hq_override=plan.q_heads_per_rank)
+    else:       # single GPU, or request-batch DP: independent requests per rank
+        w = build_workload(workload, device, seed=1234 + rank)
     B, Hq, Hkv, D, L = w["B"], w["Hq"], w["Hkv"], w["D"], w["L"]
     dt = torch.bfloat16
-    with_oproj = args.workload == "c5"
+    with_oproj = tp or workload == "c5"       # the o_proj shard belongs to the step wherever a collective follows it
     tp_group = torch.distributed.group.WORLD if world > 1 else None
-    if with_oproj:   # this rank's column shard of o_proj (bias-free, qwen2.py:166): partial sums are exact
-        w_o = torch.randn(w["hidden"], Hq * D, device=device, dtype=dt) * 0.02
-
+    w_o = torch.randn(w["hidden"], Hq * D, device=device, dtype=dt) * 0.02 if with_oproj else None
     fused_comm = None
-    if tp and args.oproj == "fused":   # K8: one kernel per rank instead of GEMM + NCCL call
+    if tp and oproj == "fused":   # K8: one kernel per rank instead of GEMM + NCCL call
         fused_comm = tp_runtime.FusedOProjAllReduce(rank, world, tp_group, hidden=w["hidden"], max_tokens=B)
+
+    def nccl_pair(out):
+        partial = torch.nn.functional.linear(out, w_o)
+        return tp_runtime.tp_all_reduce_sum(partial, tp_group) if tp else partial
 
     def after_attention(out):
         if not with_oproj:
             return out
-        if fused_comm is not None:
-            return fused_comm(out, w_o)
-        partial = torch.nn.functional.linear(out, w_o)
-        return tp_runtime.tp_all_reduce_sum(partial, tp_group) if tp else partial
-    # per-layer activations of one step, device-resident (for `value`) and pinned host copies (for `e2e`)
+        return fused_comm(out, w_o) if fused_comm is not None else nccl_pair(out)
+
     qkv_dev = [torch.randn(B, (Hq + 2 * Hkv) * D, device=device, dtype=dt) for _ in range(L)]
-    qkv_host = [t.cpu().pin_memory() for t in qkv_dev]
-    out_host = [torch.empty(B, w["hidden"] if args.workload == "c5" else Hq * D, dtype=dt).pin_memory()
-                for _ in range(L)]
-    ids_host = torch.zeros(B, dtype=torch.int64).pin_memory()
-    rpi_host = w["rpi"].cpu().pin_memory()
-    seq_host = w["seq"].cpu().pin_memory()
-    loc_host = w["out_cache_loc"].cpu().pin_memory()
     ids_dev = torch.zeros(B, dtype=torch.int64, device=device)
 
     def split(qkv):
@@ -312,34 +337,19 @@ def run_b200(args, rank, world, device):
             out = after_attention(attn_backend.SimpleAttentionBackend.forward(q, k, v, w["layers"][l], fb, True))
         return out
 
-    from baby_sglang_b200.host_staging import HostStagedAttention
-    staged = HostStagedAttention(Hq, Hkv, D, device)
-
-    def step_e2e():
-        rpi = rpi_host.to(device, non_blocking=True)
-        seq = seq_host.to(device, non_blocking=True)
-        loc = loc_host.to(device, non_blocking=True)
-        ids = ids_host.to(device, non_blocking=True)
-        fb = forward_batch.SimplifiedForwardBatch.create_decode_batch(
-            input_ids=ids, req_pool_indices=rpi, seq_lens=seq, out_cache_loc=loc,
-            req_to_token_pool=w["r2t_pool"], token_to_kv_pool=w["kv_pool"])
-        # uploads of layer l+1 and downloads of layer l overlap layer l's kernels (host_staging.py)
-        staged.forward_layers(qkv_host, out_host, w["layers"], fb, after=after_attention if with_oproj else None)
-        return out_host[L - 1]
-
     def barrier():
         if world > 1:
             torch.distributed.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
+    def timed(fn, n, nw):
+        for _ in range(nw):
             fn()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         n0 = ops.LAUNCH_COUNT
         e0.record()
-        for _ in range(steps):
+        for _ in range(n):
             fn()
         e1.record()
         barrier()
@@ -348,15 +358,42 @@ def run_b200(args, rank, world, device):
             t = torch.tensor([ms], device=device)
             torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
             ms = float(t.item())
-        return ms / steps, ops.LAUNCH_COUNT - n0
+        return ms / n, ops.LAUNCH_COUNT - n0
 
-    step_bytes = L * (decode_bytes(w["sum_seq"], B, Hq, Hkv, D) + kv_store_bytes(B, Hkv, D))
-    sampler = ClockSampler(device.index or 0)
-    if rank == 0:
+    res = dict(workload=workload, model=w["model"], B=B, Hq=Hq, Hkv=Hkv, D=D, L=L, tp=tp, mode=plan.mode,
+               with_oproj=with_oproj, hidden=w["hidden"], fused=fused_comm is not None)
+    res["step_bytes"] = L * (decode_bytes(w["sum_seq"], B, Hq, Hkv, D) + kv_store_bytes(B, Hkv, D))
+    sampler = ClockSampler(device.index or 0) if (sample_clocks and rank == 0) else None
+    if sampler:
         sampler.start()
-    ms_step, launches = timed(step_resident, args.steps, args.warmup)
-    clocks = sampler.stop() if rank == 0 else None
-    ms_e2e, _ = timed(step_e2e, args.steps, args.warmup)
+    res["ms_step"], res["launches"] = timed(step_resident, steps, warmup)
+    res["clocks"] = sampler.stop() if sampler else None
+
+    # ---- e2e: the same step through the plugin call from pinned HOST buffers
+    if with_e2e:
+        qkv_host = [t.cpu().pin_memory() for t in qkv_dev]
+        out_host = [torch.empty(B, w["hidden"] if with_oproj else Hq * D, dtype=dt).pin_memory() for _ in range(L)]
+        ids_host = torch.zeros(B, dtype=torch.int64).pin_memory()
+        rpi_host, seq_host = w["rpi"].cpu().pin_memory(), w["seq"].cpu().pin_memory()
+        loc_host = w["out_cache_loc"].cpu().pin_memory()
+        staged = HostStagedAttention(Hq, Hkv, D, device)
+
+        def step_e2e():
+            rpi = rpi_host.to(device, non_blocking=True)
+            seq = seq_host.to(device, non_blocking=True)
+            loc = loc_host.to(device, non_blocking=True)
+            ids = ids_host.to(device, non_blocking=True)
+            fb = forward_batch.SimplifiedForwardBatch.create_decode_batch(
+                input_ids=ids, req_pool_indices=rpi, seq_lens=seq, out_cache_loc=loc,
+                req_to_token_pool=w["r2t_pool"], token_to_kv_pool=w["kv_pool"])
+            # uploads of layer l+1 and downloads of layer l overlap layer l's kernels (host_staging.py)
+            staged.forward_layers(qkv_host, out_host, w["layers"], fb, after=after_attention if with_oproj else None)
+            return out_host[L - 1]
+
+        res["ms_e2e"], _ = timed(step_e2e, steps, warmup)
+        res["h2d"] = sum(t.numel() * t.element_size() for t in qkv_host) + 8 * B * 3 + 4 * B
+        res["d2h"] = sum(t.numel() * t.element_size() for t in out_host)
+        del qkv_host, out_host, staged
 
     # ---- roofline of the dominant kernel: paged_attention_kernel alone, CUDA events per launch
     md = ops.build_decode_metadata(w["r2t_pool"].req_to_token, w["rpi"], w["seq"], Hkv)
@@ -364,13 +401,13 @@ def run_b200(args, rank, world, device):
     r2t = w["r2t_pool"].req_to_token
     scale = D ** -0.5
     outbuf = torch.empty(B, Hq * D, device=device, dtype=dt)
-    reps = max(3, args.steps // 2)
+    reps = roof_reps or max(3, steps // 2)
     for l in range(L):
         ops.paged_attention(qkv_split_dev[l][0], *w["kv_pool"].get_kv_buffer(l), r2t, md.plan, scale, out=outbuf,
                             workspace=ws, merge=False)
     torch.cuda.synchronize()
     evs = []
-    for _ in range(reps):
+    for _ in range(reps * (28 // L if L < 28 else 1)):
         for l in range(L):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
@@ -379,89 +416,292 @@ def run_b200(args, rank, world, device):
             b.record()
             evs.append((a, b))
     torch.cuda.synchronize()
-    k_ms = statistics.mean(a.elapsed_time(b) for a, b in evs)
-    k_bytes = decode_bytes(w["sum_seq"], B, Hq, Hkv, D)
-    peak, peak_src = peaks()
-    achieved = k_bytes / k_ms / 1e6
+    res["k_ms"] = statistics.mean(a.elapsed_time(b) for a, b in evs)
+    res["k_bytes"] = decode_bytes(w["sum_seq"], B, Hq, Hkv, D)
 
-    allreduce = None
+    # ---- parity at the timed size: layer 0 of the step (store, attend, merge) vs the oracle on sampled requests
+    fb = forward_batch.SimplifiedForwardBatch.create_decode_batch(
+        input_ids=ids_dev, req_pool_indices=w["rpi"], seq_lens=w["seq"], out_cache_loc=w["out_cache_loc"],
+        req_to_token_pool=w["r2t_pool"], token_to_kv_pool=w["kv_pool"])
+    q0, k0, v0 = qkv_split_dev[0]
+    attn0 = attn_backend.SimpleAttentionBackend.forward(q0, k0, v0, w["layers"][0], fb, True)
+    torch.cuda.synchronize()
+    ks, vs = w["kv_pool"].get_kv_buffer(0)
+    par = SC.decode_rows(q0, ks, vs, r2t, w["rpi"], w["seq"], attn0, SC.pick_requests(w["seq"], 16, seed=3))
+    loc = w["out_cache_loc"].long()
+    par["kv_store_bit_exact"] = bool(torch.equal(ks[loc], k0) and torch.equal(vs[loc], v0))
+    if tp:   # the collective: fused K8 (or the NCCL pair) against fp32 sums of every rank's partial
+        got = after_attention(attn0).float()
+        ref32 = torch.nn.functional.linear(attn0.float(), w_o.float())
+        torch.distributed.all_reduce(ref32)
+        par["oproj_allreduce_max_abs_err"] = float((got - ref32).abs().max())
+        par["oproj_allreduce_ref_absmax"] = float(ref32.abs().max())
+        same = got.clone()
+        torch.distributed.broadcast(same, src=0)
+        par["oproj_allreduce_identical_on_all_ranks"] = bool(torch.equal(same, got))
+        t = torch.tensor([par["max_abs_err"], par["oproj_allreduce_max_abs_err"],
+                          0.0 if par["kv_store_bit_exact"] else 1.0,
+                          0.0 if par["oproj_allreduce_identical_on_all_ranks"] else 1.0], device=device)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        par["max_abs_err"], par["oproj_allreduce_max_abs_err"] = float(t[0]), float(t[1])
+        par["kv_store_bit_exact"] = t[2].item() == 0.0
+        par["oproj_allreduce_identical_on_all_ranks"] = t[3].item() == 0.0
+        par["oproj_tol"] = "one bf16 ulp of the fp32 sum"
+    par.update(tol=TOL, ok=par["max_abs_err"] <= TOL and par["kv_store_bit_exact"])
+    res["parity_check"] = par
+
+    # ---- the collective alone (NCCL) and K8 alone, for the sharded report
+    res["allreduce"] = None
     if tp:
         buf = torch.randn(B, w["hidden"], device=device, dtype=dt)
-        for _ in range(5):
+
+        def ar():
             tp_runtime.tp_all_reduce_sum(buf, tp_group)
-        barrier()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        n_ar = 20
-        a.record()
-        for _ in range(n_ar):
-            tp_runtime.tp_all_reduce_sum(buf, tp_group)
-        b.record()
-        barrier()
-        t = torch.tensor([a.elapsed_time(b) / n_ar], device=device)
-        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-        ar_ms = float(t.item())
+        ar_ms, _ = timed(ar, 20, 5)
         nbytes = buf.numel() * buf.element_size()
-        allreduce = {"bytes": nbytes, "avg_ms": round(ar_ms, 5),
-                     "busbw_GBps": round(2 * (world - 1) / world * nbytes / ar_ms / 1e6, 1),
-                     "backend": "NCCL over NVLink/NVSwitch (torch.distributed all_reduce SUM)"}
-    used_fused = fused_comm is not None
-    if used_fused:
+        res["allreduce"] = {"bytes": nbytes, "nccl_avg_us": round(ar_ms * 1e3, 2),
+                            "nccl_busbw_GBps": round(2 * (world - 1) / world * nbytes / ar_ms / 1e6, 1),
+                            "backend": "NCCL over NVLink/NVSwitch (torch.distributed all_reduce SUM)"}
+        x = torch.randn(B, Hq * D, device=device, dtype=dt)
+        pair_ms, _ = timed(lambda: nccl_pair(x), 20, 5)
+        res["allreduce"]["linear_plus_nccl_us"] = round(pair_ms * 1e3, 2)
+        if fused_comm is not None:
+            k8_ms, _ = timed(lambda: fused_comm(x, w_o), 20, 5)
+            res["allreduce"]["k8_fused_us"] = round(k8_ms * 1e3, 2)
+            res["allreduce"]["k8_busbw_GBps"] = round(2 * (world - 1) / world * nbytes / k8_ms / 1e6, 1)
+            res["allreduce"]["k8_exchange"] = fused_comm.exchange
+    if fused_comm is not None:
         fused_comm.close()      # collective (barrier): every rank, before the others leave
+    del w, qkv_dev, qkv_split_dev, fb, attn0
+    _free()
+    return res
+
+
+# ------------------------------------------------------------------------------------------------
+# the other half of the metric: decode tok/s through the unchanged scheduler + model on the drop-in path
+# ------------------------------------------------------------------------------------------------
+def measure_decode_tok_s(device, steps=64, batch=256, ctx=4096):
+    from baby_sglang_b200 import DROPIN_DIR, model_hooks
+    from baseline import ref_loader, ref_stack
+    if ref_loader.find_reference() is None:
+        return {"unavailable": "no reference checkout (baseline/_ref not staged: scripts/stage_reference.py)"}
+    Hq, Hkv, D, L, hidden, inter, vocab = GEOMETRY["qwen2.5-7b"]
+    cfg = dict(hidden_size=hidden, num_attention_heads=Hq, num_key_value_heads=Hkv, intermediate_size=inter,
+               num_hidden_layers=L, vocab_size=vocab)
+    pool = dict(max_total_tokens=batch * (ctx + steps), max_requests=batch)     # SURVEY §8d NS row: 256 * 4160
+    out = {"workload": f"qwen2.5-7b geometry, random init, bf16, B={batch}, ctx {ctx}, {steps} greedy decode steps "
+                       f"through the reference's unchanged Scheduler loop body (scheduler.py:137-163) and "
+                       f"BabyQwen2ForCausalLM on the drop-in modules; MAX_REQUESTS={batch}, "
+                       f"MAX_TOTAL_TOKENS={pool['max_total_tokens']}",
+           "state": "decode phase seeded directly (baseline/ref_stack.seed_decode_state): the reference's own "
+                    "prefill would need 319 GB of logits at this size",
+           "unit": "tok/s", "variants": {}}
+    run = ref_stack.build(DROPIN_DIR, cfg, str(device), torch.bfloat16, **pool, listen=False, init="device")
+    model = run.model
+    ids_ref = None
+    for name, hooks in (("dropin", ()), ("dropin+K5K6K7", ("rope", "sampler", "prep")),
+                        ("dropin+K5K6K7+cuda_graph", ("rope", "sampler", "prep", "graph"))):
+        sched = run.stack.scheduler.Scheduler(model, tokenizer=None)          # fresh pools for every variant
+        run.scheduler = sched
+        model_hooks.uninstall_cuda_graph_decode(model)
+        model_hooks.uninstall_fused_rope_kv_store(model)
+        if "rope" in hooks:
+            model_hooks.install_fused_rope_kv_store(model)
+        if "sampler" in hooks:
+            model_hooks.install_batched_greedy_sampler(sched)
+        if "prep" in hooks:
+            model_hooks.install_device_batch_prep(sched)
+        if "graph" in hooks:
+            model_hooks.install_cuda_graph_decode(model)
+        ref_stack.seed_decode_state(run, batch, ctx, steps + 4, seed=0)
+        r = ref_stack.timed_decode_steps(run, steps - 2, warmup=2)
+        med = statistics.median(r["host_ms"])
+        v = {"ms_per_step_median": round(med, 3), "ms_per_step_mean": round(statistics.mean(r["host_ms"]), 3),
+             "device_ms_per_step_median": round(statistics.median(r["dev_ms"]), 3),
+             "decode_tok_per_s": round(batch / (med / 1e3), 1)}
+        if ids_ref is None:
+            ids_ref = r["ids"]
+        else:   # same seeded state, same weights: the hooks must not change a sampled token
+            v["first_step_ids_identical_to_dropin"] = r["ids"][0] == ids_ref[0]
+            v["steps_with_identical_ids"] = sum(a == b for a, b in zip(r["ids"], ids_ref))
+        out["variants"][name] = v
+        model_hooks.uninstall_cuda_graph_decode(model)
+        model_hooks.uninstall_fused_rope_kv_store(model)
+        del sched
+        run.scheduler = None
+        _free()
+    best = max(out["variants"].values(), key=lambda x: x["decode_tok_per_s"])
+    out["value"] = best["decode_tok_per_s"]
+    out["best_variant"] = [k for k, x in out["variants"].items() if x is best][0]
+    del run, model
+    _free()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# K1 / K5 / K6: HBM-bound byte kernels either side of the path
+# ------------------------------------------------------------------------------------------------
+def measure_small_kernels(device):
+    from baby_sglang_b200 import ops
+    peak, _ = peaks()
+    Hq, Hkv, D = GEOMETRY["qwen2.5-7b"][:3]
+    vocab = GEOMETRY["qwen2.5-7b"][6]
+    dt = torch.bfloat16
+    out = {}
+
+    def timeit(fn, reps=30, flush=None):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(reps):
+            if flush is not None:
+                flush.zero_()                # > L2: evicts the kernel's inputs between timed launches
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        return statistics.median(ts)
+
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=device)
+    for T in (256, 16384):
+        S = 1 << 20
+        ks = torch.empty(S + 1, Hkv, D, device=device, dtype=dt)
+        vs = torch.empty(S + 1, Hkv, D, device=device, dtype=dt)
+        loc = (torch.randperm(S, device=device)[:T] + 1).to(torch.int32)
+        qkv = torch.randn(T, (Hq + 2 * Hkv) * D, device=device, dtype=dt)
+        q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+        k, v = k.contiguous().view(T, Hkv, D), v.view(T, Hkv, D)
+        ms = timeit(lambda: ops.kv_store(ks, vs, loc, k, v), flush=flush)
+        nb = kv_store_bytes(T, Hkv, D)
+        out[f"K1_kv_store_T{T}"] = {"bytes": nb, "us": round(ms * 1e3, 2), "GBps": round(nb / ms / 1e6, 1),
+                                    "frac_of_hbm_peak": round(nb / ms / 1e6 / peak, 4)}
+        pos = torch.randint(0, 4096, (T,), device=device)
+        inv = 1.0 / (1e6 ** (torch.arange(0, D, 2, device=device).float() / D))
+        ms = timeit(lambda: ops.rope_kv_store(qkv, pos, inv, Hq, Hkv, D, ks, vs, loc), flush=flush)
+        nb = 2 * T * (Hq + 2 * Hkv) * D * 2 + 12 * T
+        out[f"K5_rope_kv_store_T{T}"] = {"bytes": nb, "us": round(ms * 1e3, 2), "GBps": round(nb / ms / 1e6, 1),
+                                         "frac_of_hbm_peak": round(nb / ms / 1e6 / peak, 4)}
+        del ks, vs, qkv
+    logits = torch.randn(256, vocab, device=device, dtype=dt)
+    ms = timeit(lambda: ops.greedy_sample(logits), flush=flush)
+    nb = logits.numel() * 2 + 8 * 256
+    out["K6_greedy_sample_B256"] = {"bytes": nb, "us": round(ms * 1e3, 2), "GBps": round(nb / ms / 1e6, 1),
+                                    "frac_of_hbm_peak": round(nb / ms / 1e6 / peak, 4)}
+    out["note"] = ("CUDA events per launch, median of 30, a 512 MiB buffer zeroed between launches (inputs evicted "
+                   "from L2); bytes = SURVEY §8d formulas (K1: 2*(2*T*Hkv*D*e)+4T; K5: read + write of the fused "
+                   "row; K6: B*V*e).  At T=256 these are launch-latency bound (a few us of work).")
+    del flush, logits
+    _free()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# the GPU arm
+# ------------------------------------------------------------------------------------------------
+def run_b200(args, rank, world, device):
+    extend = None
+    if world == 1 and rank == 0 and not args.skip_extend:
+        # K3 is timed alone and first, like the burst peak it is compared with (after the 28-layer decode loop the
+        # GPU sits at its power cap and the same kernel runs ~10 % slower).
+        extend = measure_extend_c3(device)
+        _free()
+    main = measure_decode_workload(args.workload, rank, world, device, args.steps, args.warmup, oproj=args.oproj,
+                                   sample_clocks=True)
+    sharded = None
+    if args.workload == "ns" and not args.skip_sharded:
+        # config C5 in the same line, so the driver's SCALE run records the sharded-with-collective configuration
+        s = measure_decode_workload("c5", rank, world, device, max(5, min(args.steps, 20)), 3, oproj=args.oproj,
+                                    with_e2e=False, roof_reps=1)
+        peak, _ = peaks()
+        sharded = {
+            "workload": f"{s['model']} decode (config C5): B={s['B']}, ctx U[512,8192], {s['Hq']}q/{s['Hkv']}kv per "
+                        f"rank, one layer per step (K1, K2, K2c, o_proj shard"
+                        + (" + all-reduce" if s["tp"] else "") + ")",
+            "parallelism": f"KV-head TP x{world}" if s["tp"] else "single GPU",
+            "oproj": ("K8 fused GEMM + all-reduce" if s["fused"] else "F.linear + NCCL all-reduce") if s["tp"]
+            else "F.linear (full o_proj)",
+            "ms_per_step": round(s["ms_step"], 4),
+            "aggregate_GBps": round(world * s["step_bytes"] / s["ms_step"] / 1e6, 1),
+            "decode_tok_per_s_attention_path": round(s["B"] / (s["ms_step"] / 1e3), 1),
+            "k2_ms_per_rank": round(s["k_ms"], 5),
+            "k2_frac_of_hbm_peak": round(s["k_bytes"] / s["k_ms"] / 1e6 / peak, 4),
+            "allreduce": s["allreduce"], "parity_check": s["parity_check"]}
+    tok = small = None
+    if world == 1 and rank == 0:
+        if args.workload == "ns" and not args.skip_model:
+            try:
+                tok = measure_decode_tok_s(device)
+            except Exception as e:   # the headline line must survive a failure of the model-level leg
+                tok = {"error": repr(e)[:500]}
+                _free()
+        if not args.skip_small:
+            small = measure_small_kernels(device)
     if rank != 0:
         return
-    cpu = cpu_baseline(args.workload, seconds=12.0)
-    value = world * step_bytes / ms_step / 1e6
-    e2e_v = world * step_bytes / ms_e2e / 1e6
-    h2d = sum(t.numel() * t.element_size() for t in qkv_host) + 8 * B * 3 + 4 * B
-    d2h = sum(t.numel() * t.element_size() for t in out_host)
+    cpu = cpu_baseline(args.workload, seconds=15.0)
+    m = main
+    tp, L, B = m["tp"], m["L"], m["B"]
+    peak, peak_src = peaks()
+    achieved = m["k_bytes"] / m["k_ms"] / 1e6
+    total = (1 if tp else world) * m["step_bytes"] * (world if tp else 1)      # whole-job bytes either way
+    value = total / m["ms_step"] / 1e6
+    lo, hi = WORKLOADS[args.workload][2], WORKLOADS[args.workload][3]
+    if tp:
+        par = (f"KV-head TP x{world} (tp_runtime.plan_parallelism): o_proj partial + " +
+               ("SUM all-reduce fused in one kernel over NVLink (K8)" if m["fused"] else "NCCL all-reduce") +
+               " per layer, inside the timed step")
+    elif world > 1:
+        par = f"request-batch DP x{world} (tp_runtime.plan_parallelism: Hkv {m['Hkv']} < {world}; no collective)"
+    else:
+        par = "single GPU"
     line = {
         "metric": METRIC if args.workload == "ns" else f"paged decode attn HBM GB/s, workload {args.workload}",
         "value": round(value, 1), "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong" if tp else "weak",
+        "ms_per_step": round(m["ms_step"], 4), "higher_is_better": True, "scaling": "strong" if tp else "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"{w['model']} paged GQA decode ({Hq}q/{Hkv}kv{' per rank' if tp else ''}, D={D}), "
-                               f"batch {B}{'' if tp else '/GPU'}, "
-                               f"ctx {WORKLOADS[args.workload][2]}..{WORKLOADS[args.workload][3]}, page_size 1, "
-                               f"{L} layers/step, fragmented page table",
-                   "parallelism": (f"KV-head TP x{world}: o_proj partial + "
-                                   + ("all-reduce fused in one kernel over NVLink peer memory (K8)" if used_fused
-                                      else "NCCL all-reduce per layer") if tp else
-                                   "request-batch DP (no collective)" if world > 1 else "single GPU"),
-                   "l2": f"inputs > L2: {k_bytes / 1e9:.2f} GB of KV per layer, {L} distinct layers per step",
+        "config": {"workload": f"{m['model']} paged GQA decode ({m['Hq']}q/{m['Hkv']}kv{' per rank' if tp else ''}, "
+                               f"D={m['D']}), batch {B}{'' if tp or world == 1 else '/GPU'}, ctx {lo}..{hi}, "
+                               f"page_size 1, {L} layers/step, fragmented page table",
+                   "parallelism": par,
+                   "l2": f"inputs > L2: {m['k_bytes'] / 1e9:.2f} GB of KV per layer per rank, {L} distinct layers "
+                         f"per step",
                    "step": "K4 metadata + per layer (K1 kv_store, K2 paged attention, K2c merge"
-                           + (", o_proj shard GEMM" + (", all-reduce" if tp else "") if with_oproj else "") + ")"},
-        "allreduce": allreduce,
-        "decode_tok_per_s_attention_path": round(world * B / (ms_step / 1e3), 1),
-        "e2e": {"value": round(e2e_v, 1), "unit": "GB/s", "ms_per_step": round(ms_e2e, 4),
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "api": "HostStagedAttention.forward_layers (dropin attn_backend.SimpleAttentionBackend.forward per layer) from pinned host q/k/v, copies on side streams"},
-        "gpu_launches": launches,
-        "clocks": clocks,
+                           + (", o_proj shard GEMM" + (" + all-reduce" if tp else "") if m["with_oproj"] else "")
+                           + ")"},
+        "decode_tok_per_s": tok,
+        "decode_tok_per_s_attention_path": round((1 if tp else world) * B / (m["ms_step"] / 1e3), 1),
+        "e2e": {"value": round(total / m["ms_e2e"] / 1e6, 1), "unit": "GB/s", "ms_per_step": round(m["ms_e2e"], 4),
+                "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": m["d2h"],
+                "api": "HostStagedAttention.forward_layers (dropin attn_backend.SimpleAttentionBackend.forward per "
+                       "layer) from pinned host q/k/v, copies on side streams"},
+        "gpu_launches": m["launches"],
+        "clocks": m["clocks"],
         "roofline": {"bound": "hbm", "kernel": "paged_attention_kernel", "achieved": round(achieved, 1),
                      "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "peak_source": peak_src,
-                     "bytes_per_launch": k_bytes, "avg_launch_ms": round(k_ms, 5),
+                     "bytes_per_launch": m["k_bytes"], "avg_launch_ms": round(m["k_ms"], 5),
                      "traffic": args.traffic if args.traffic is not None else
                      (traffic_from_profiles(args.workload) if world == 1 else None)},
+        "parity_check": m["parity_check"],
+        "allreduce": m["allreduce"],
+        "sharded": sharded,
         "extend_roofline": extend,
+        "small_kernels": small,
         "cpu_baseline": cpu,
     }
-    if used_fused:
-        line["oproj"] = {"impl": "K8 oproj_allreduce_kernel (tcgen05 GEMM + owner-reduce over NVLink peer memory)",
-                         "replaces": "F.linear + NCCL all-reduce (bench.py --oproj nccl)"}
     print(json.dumps(line), flush=True)
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU arm: the oracle (port of the reference's torch path) on the box's host cores
+# CPU arm: the reference's own modules (when reachable) or the oracle port, on the box's host cores
 # ------------------------------------------------------------------------------------------------
-def cpu_baseline(workload, seconds=12.0, sample_batch=8):
-    from oracle import paged_attention_oracle as O
+def _cpu_case(workload, Bs, seed=0):
     model, B, lo, hi, L = WORKLOADS[workload]
-    Hq, Hkv, D, _, _ = GEOMETRY[model]
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    g = torch.Generator().manual_seed(0)
-    Bs = min(sample_batch, B)
+    Hq, Hkv, D = GEOMETRY[model][:3]
+    g = torch.Generator().manual_seed(seed)
+    Bs = min(Bs, B)
     seq = torch.full((Bs,), lo, dtype=torch.int64) if lo == hi else torch.randint(lo, hi + 1, (Bs,), generator=g)
     S = int(seq.sum()) + 16
     C = int(seq.max()) + 8
@@ -480,27 +720,80 @@ def cpu_baseline(workload, seconds=12.0, sample_batch=8):
     k = torch.randn(Bs, Hkv, D, generator=g)
     v = torch.randn(Bs, Hkv, D, generator=g)
     nbytes = decode_bytes(int(seq.sum()), Bs, Hq, Hkv, D) + kv_store_bytes(Bs, Hkv, D)
-    O.backend_forward(q, k, v, k_slab, v_slab, r2t, rpi, seq, loc, False)      # warm-up
+    return dict(B=B, Bs=Bs, Hq=Hq, Hkv=Hkv, D=D, L=L, lo=lo, hi=hi, seq=seq, S=S, C=C, k_slab=k_slab, v_slab=v_slab,
+                r2t=r2t, rpi=rpi, loc=loc, q=q, k=k, v=v, nbytes=nbytes)
+
+
+def _reference_layer_call(c):
+    """The reference's own SimpleAttentionBackend.forward on its own pools (attn_backend.py:8-149), or None."""
+    from baseline import ref_loader
+    if ref_loader.find_reference() is None:
+        return None
+    ref = ref_loader.load_stack(names=("memory_pool", "forward_batch", "attn_backend"))
+    kv = ref.memory_pool.MHATokenToKVPool(size=c["S"], dtype=torch.float32, head_num=c["Hkv"], head_dim=c["D"],
+                                          layer_num=1, device="cpu")
+    kv.k_buffer[0].copy_(c["k_slab"])
+    kv.v_buffer[0].copy_(c["v_slab"])
+    r2t = ref.memory_pool.ReqToTokenPool(size=c["Bs"], max_context_len=c["C"], device="cpu")
+    r2t.req_to_token.copy_(c["r2t"])
+    fb = ref.forward_batch.SimplifiedForwardBatch.create_decode_batch(
+        input_ids=torch.zeros(c["Bs"], dtype=torch.int64), req_pool_indices=c["rpi"], seq_lens=c["seq"],
+        out_cache_loc=c["loc"], req_to_token_pool=r2t, token_to_kv_pool=kv)
+    layer = _Layer(0, c["Hq"], c["Hkv"], c["D"])
+    fwd = ref.attn_backend.SimpleAttentionBackend.forward
+    return lambda: fwd(c["q"], c["k"], c["v"], layer, fb, True)
+
+
+def cpu_baseline(workload, seconds=15.0, sample_batch=64):
+    """One layer call (kv_store + decode attention) of the workload on the host cores, fp32, all threads, on
+    `sample_batch` of the requests, repeated for about `seconds`.  kind "reference" = the reference's own modules
+    from the staged checkout; else the oracle port."""
+    from oracle import paged_attention_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    c = _cpu_case(workload, sample_batch)
+    call = _reference_layer_call(c)
+    kind = "reference" if call is not None else "port"
+    if call is None:
+        def call():
+            return O.backend_forward(c["q"], c["k"], c["v"], c["k_slab"], c["v_slab"], c["r2t"], c["rpi"], c["seq"],
+                                     c["loc"], False)
+    call()      # warm-up
     t0 = time.perf_counter()
     n = 0
     while True:
-        O.backend_forward(q, k, v, k_slab, v_slab, r2t, rpi, seq, loc, False)
+        call()
         n += 1
         dt = time.perf_counter() - t0
         if dt >= seconds or n >= 200:
             break
-    return {"value": round(n * nbytes / dt / 1e9, 4), "unit": "GB/s", "cores": cores, "kind": "port",
-            "ms_per_layer_call": round(dt / n * 1e3, 3),
-            "sample": f"{n} calls of one layer (kv_store + decode attention) on {Bs} of the {B} requests, "
-                      f"ctx {lo}..{hi}, fp32 (reference CPU dtype), oracle/paged_attention_oracle.py"}
+    ms_call = dt / n * 1e3
+    # a STEP of the workload is L layers x B requests; the sample is one layer x Bs requests
+    ms_step_est = ms_call * c["L"] * c["B"] / c["Bs"]
+    out = {"value": round(n * c["nbytes"] / dt / 1e9, 4), "unit": "GB/s", "cores": cores, "kind": kind,
+           "ms_per_layer_call_on_sample": round(ms_call, 3), "ms_per_step_extrapolated": round(ms_step_est, 1),
+           "decode_tok_per_s_attention_path": round(c["B"] / (ms_step_est / 1e3), 2),
+           "sample": f"{n} calls of one layer (kv_store + decode attention) on {c['Bs']} of the {c['B']} requests, "
+                     f"ctx {c['lo']}..{c['hi']}, fp32 (the reference's CPU dtype, model_loader.py:56-64), "
+                     + ("the reference's own attn_backend/memory_pool/forward_batch from the staged checkout"
+                        if kind == "reference" else "oracle/paged_attention_oracle.py")}
+    if kind == "reference":     # the port beside it, same sample, for continuity with round 1
+        t0 = time.perf_counter()
+        m = 0
+        while m < 3 or time.perf_counter() - t0 < min(4.0, seconds / 3):
+            O.backend_forward(c["q"], c["k"], c["v"], c["k_slab"], c["v_slab"], c["r2t"], c["rpi"], c["seq"],
+                              c["loc"], False)
+            m += 1
+        out["oracle_port_GBps_same_sample"] = round(m * c["nbytes"] / (time.perf_counter() - t0) / 1e9, 4)
+    return out
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU implementation of the path = the oracle port (the
-    Python reference cannot travel to the GPU box), all host threads, bounded sample per step."""
+    """--impl reference: the reference's CPU implementation of the path (its own modules from the staged checkout,
+    else the oracle port), all host threads, a bounded sample per step."""
     if rank != 0:
         return
-    per = max(2.0, min(20.0, 90.0 / max(1, args.steps + args.warmup)))
+    per = max(3.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
     vals = []
     for i in range(args.warmup + args.steps):
         r = cpu_baseline(args.workload, seconds=per)
@@ -508,15 +801,17 @@ def run_reference(args, rank, world):
             vals.append(r)
     v = statistics.mean(x["value"] for x in vals)
     model, B, lo, hi, L = WORKLOADS[args.workload]
-    Hq, Hkv, D, _, _ = GEOMETRY[model]
+    Hq, Hkv, D = GEOMETRY[model][:3]
     line = {
         "impl": "reference",
         "metric": METRIC if args.workload == "ns" else f"paged decode attn HBM GB/s, workload {args.workload}",
         "value": round(v, 4), "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": round(statistics.mean(x["ms_per_layer_call"] for x in vals), 3),
+        "ms_per_step": round(statistics.mean(x["ms_per_step_extrapolated"] for x in vals), 1),
+        "ms_per_step_note": "one step = 28 layers x 256 requests, extrapolated per byte from the timed sample "
+                            "(one layer call on 64 requests); the sample's own time is in cpu_baseline",
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{model} paged GQA decode ({Hq}q/{Hkv}kv, D={D}), ctx {lo}..{hi}, page_size 1; "
-                               f"CPU port of the reference path on a bounded sample"},
+        "config": {"workload": f"{model} paged GQA decode ({Hq}q/{Hkv}kv, D={D}), batch {B}, ctx {lo}..{hi}, "
+                               f"page_size 1, {L} layers/step; the reference's CPU path on a bounded sample"},
         "cpu_baseline": {**vals[-1], "value": round(v, 4)},
         "e2e": {"value": round(v, 4), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -532,10 +827,12 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="ns", choices=sorted(WORKLOADS))
     ap.add_argument("--oproj", default="fused", choices=["fused", "nccl"],
-                    help="c5 under TP: K8 (o_proj GEMM with the all-reduce fused over NVLink peer memory) or "
+                    help="under KV-head TP: K8 (o_proj GEMM with the all-reduce fused over NVLink) or "
                          "F.linear + NCCL all-reduce")
     ap.add_argument("--traffic", type=float, default=None,
                     help="dram bytes per launch of the dominant kernel from an ncu --set full capture (profiles/)")
+    for flag in ("extend", "sharded", "model", "small"):
+        ap.add_argument(f"--skip-{flag}", action="store_true", help=f"leave the `{flag}` leg out (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -48,17 +48,28 @@ def _prompts(vocab, lens, seed):
     return [torch.randint(0, vocab, (n,), generator=g) for n in lens]
 
 
-def _run(run: "ref_stack.StackRun", prompts, mode, n_new=N_NEW):
+def _run(run: "ref_stack.StackRun", prompts, mode, n_new=N_NEW, forced=None):
+    """Cold run + radix-hit rerun.  `forced` = [ids of the cold run, ids of the rerun] of another stack: this
+    stack's own argmax is recorded but the other stack's tokens are fed forward (normal mode only)."""
     sp = run.stack.sample.SamplingParams(max_new_tokens=n_new, do_sample=False, eos_id=-1)
     fn = run.scheduler.run_batch if mode == "normal" else run.scheduler.run_batch_overlap
+    forcer = None
+    if forced is not None:
+        assert mode == "normal"
+        forcer = getattr(run, "forcer", None)
+        if forcer is None:
+            forcer = run.forcer = ref_stack.Forcer(run.scheduler)
     out = []
-    for _ in ("cold", "radix-hit"):
+    for phase in range(2):
         if run.tracker is not None:
             run.tracker.start_run()
+        if forcer is not None:
+            forcer.start_run(prompts, forced[phase])
         ids = fn([p.clone() for p in prompts], sp)
         ids = [[int(t) for t in r] for r in ids]
         margins = run.tracker.margins(prompts) if run.tracker is not None else None
-        out.append((ids, margins, run.state()))
+        own = [list(x) for x in forcer.own] if forcer is not None else None
+        out.append((ids, margins, run.state(), own))
     return out
 
 
@@ -73,22 +84,49 @@ def _append_flip_log(entry):
         json.dump(data, f, indent=1)
 
 
-def _compare(case, ref_runs, got_runs):
+def _same_state(case, phase, rstate, gstate):
+    for key in ("req_to_token", "free_slots"):
+        assert torch.equal(rstate[key], gstate[key]), f"{case} {phase}: {key} differs"
+    for key in ("free_rows", "evictable_size", "kv_available"):
+        assert rstate[key] == gstate[key], f"{case} {phase}: {key} {rstate[key]} vs {gstate[key]}"
+
+
+def _compare_free(case, ref_runs, got_runs):
+    """Free-running: each request identical for all 64 steps, or parting from the reference at a tie.  Once a
+    request has parted, its later tokens -- and through them the radix tree's node sizes -- legitimately differ,
+    so the index state is compared only while no request has parted (the forced comparison pins it always)."""
+    parted = False
     for phase, (r, g) in zip(("cold", "radix-hit"), zip(ref_runs, got_runs)):
-        (rids, rmarg, rstate), (gids, _, gstate) = r, g
-        for key in ("req_to_token", "free_slots"):
-            assert torch.equal(rstate[key], gstate[key]), f"{case} {phase}: {key} differs"
-        for key in ("free_rows", "evictable_size", "kv_available"):
-            assert rstate[key] == gstate[key], f"{case} {phase}: {key} {rstate[key]} vs {gstate[key]}"
+        (rids, rmarg, rstate, _), (gids, _, gstate, _) = r, g
         assert all(len(x) == N_NEW for x in rids) and all(len(x) == N_NEW for x in gids)
         assert all(len(m) == N_NEW for m in rmarg), "recorder lost a step"
         res = ref_stack.classify_divergence(rids, gids, rmarg)
-        _append_flip_log({"case": f"{case}/{phase}", "steps_total": res["steps_total"],
+        _append_flip_log({"case": f"{case}/free/{phase}", "steps_total": res["steps_total"],
                           "identical_requests": sum(a == b for a, b in zip(rids, gids)), "requests": len(rids),
                           "ties": res["ties"], "mismatches": res["mismatches"]})
         assert not res["mismatches"], f"{case} {phase}: greedy IDs differ away from a tie: {res['mismatches'][:3]}"
-        print(f"[real-stack] {case} {phase}: {sum(a == b for a, b in zip(rids, gids))}/{len(rids)} requests identical "
-              f"over {N_NEW} steps; tie departures: {[(t['request'], t['step'], round(t['ref_margin'], 5)) for t in res['ties']]}")
+        parted = parted or bool(res["ties"])
+        if not parted:
+            _same_state(case, phase, rstate, gstate)
+        print(f"[real-stack] {case} free {phase}: {sum(a == b for a, b in zip(rids, gids))}/{len(rids)} requests "
+              f"identical over {N_NEW} steps; tie departures (request, step, margin): "
+              f"{[(t['request'], t['step'], round(t['ref_margin'], 5)) for t in res['ties']]}")
+
+
+def _compare_forced(case, ref_runs, got_runs):
+    """Teacher-forced: index state bit-exact after every run, and the stack's own argmax equal to the reference's
+    token at EVERY step of every request, ties (reference margin <= 2 bf16 ulps) excepted and logged."""
+    for phase, (r, g) in zip(("cold", "radix-hit"), zip(ref_runs, got_runs)):
+        (rids, rmarg, rstate, _), (gids, _, gstate, own) = r, g
+        assert gids == rids, "forcing did not keep the trajectory"
+        _same_state(case, phase, rstate, gstate)
+        res = ref_stack.classify_forced(rids, own, rmarg)
+        _append_flip_log({"case": f"{case}/forced/{phase}", "steps_total": res["steps_total"],
+                          "steps_equal": res["steps_equal"], "ties": res["ties"], "mismatches": res["mismatches"]})
+        assert not res["mismatches"], f"{case} {phase}: argmax differs away from a tie: {res['mismatches'][:3]}"
+        print(f"[real-stack] {case} forced {phase}: {res['steps_equal']}/{res['steps_total']} steps identical, "
+              f"{len(res['ties'])} ties (margins {[round(t['ref_margin'], 5) for t in res['ties']]}); index state "
+              f"bit-exact")
 
 
 # ----------------------------------------------------------------------------------------------- CPU
@@ -131,6 +169,16 @@ def test_recorder_and_tracker_on_the_pure_reference_cpu():
     assert len(res["ties"]) + len(res["mismatches"]) == 1
     marg[1][4] = [1.0, 1.0]
     assert len(ref_stack.classify_divergence(want, forged, marg)["ties"]) == 1
+    # teacher forcing: a second pure-reference stack fed a DIFFERENT trajectory follows it, records its own argmax,
+    # and ends in the same index state as a stack that produced that trajectory itself would have sizes for
+    other = ref_stack.build(None, TINY, "cpu", torch.float32, 4096, 8, listen=False)
+    forcer = ref_stack.Forcer(other.scheduler)
+    forcer.start_run(prompts, forged)
+    assert other.scheduler.run_batch([p.clone() for p in prompts], sp) == forged
+    assert forcer.own[0] == want[0] and forcer.own[2] == want[2]        # untouched requests predict the same
+    assert forcer.own[1][:5] == want[1][:5]                             # ... and so does request 1 up to the forgery
+    res = ref_stack.classify_forced(want, forcer.own, marg)
+    assert not res["mismatches"] or all(m["request"] == 1 and m["step"] > 4 for m in res["mismatches"])
 
 
 # ----------------------------------------------------------------------------------------------- GPU
@@ -143,14 +191,17 @@ def test_unchanged_stack_on_dropins_matches_pure_reference(name, mode):
     prompts = _prompts(cfg["vocab_size"], lens, seed=len(name))
     ref = ref_stack.build(None, cfg, "cuda", torch.bfloat16, **POOL)
     ref_runs = _run(ref, prompts, mode)
-    got = ref_stack.build(DROPIN_DIR, cfg, "cuda", torch.bfloat16, **POOL, listen=False)
-    assert type(got.scheduler.token_to_kv_pool).__module__ == "memory_pool"
-    assert got.stack.attn_backend.__file__.startswith(DROPIN_DIR)
-    _compare(f"{name}/{mode}/dropin", ref_runs, _run(got, prompts, mode))
-    del got
-    hooked = ref_stack.build(DROPIN_DIR, cfg, "cuda", torch.bfloat16, **POOL, listen=False,
-                             hooks=("rope", "sampler", "prep"))
-    _compare(f"{name}/{mode}/dropin+K5K6K7", ref_runs, _run(hooked, prompts, mode))
+    ref_ids = [r[0] for r in ref_runs]
+    for label, hooks in (("dropin", ()), ("dropin+K5K6K7", ("rope", "sampler", "prep"))):
+        got = ref_stack.build(DROPIN_DIR, cfg, "cuda", torch.bfloat16, **POOL, listen=False, hooks=hooks)
+        assert type(got.scheduler.token_to_kv_pool).__module__ == "memory_pool"
+        assert got.stack.attn_backend.__file__.startswith(DROPIN_DIR)
+        _compare_free(f"{name}/{mode}/{label}", ref_runs, _run(got, prompts, mode))
+        del got
+        if mode == "normal":     # the overlap worker samples on its own thread: free-running only
+            forced = ref_stack.build(DROPIN_DIR, cfg, "cuda", torch.bfloat16, **POOL, listen=False, hooks=hooks)
+            _compare_forced(f"{name}/{mode}/{label}", ref_runs, _run(forced, prompts, mode, forced=ref_ids))
+            del forced
 
 
 @needs_ref
@@ -158,20 +209,26 @@ def test_unchanged_stack_on_dropins_matches_pure_reference(name, mode):
 def test_unchanged_stack_shared_prefixes_and_eviction():
     """Prompts that share prefixes (shared radix nodes -> aliased page-table cells, `cache_unfinished_req` cell
     rewrites, duplicate-slot frees, radix_cache.py:174-205) in a pool small enough that the radix cache must EVICT
-    between waves (scheduler.py:409-421), but never retract: index state and IDs as above."""
+    between waves (scheduler.py:409-421), but never retract.  Teacher-forced, so the radix tree holds the same
+    token sequences in both stacks and the index state must stay bit-exact through every wave."""
     cfg, _ = GEOMETRIES["qwen7b_heads"]
     g = torch.Generator().manual_seed(7)
     base = torch.randint(0, cfg["vocab_size"], (400,), generator=g)
     prompts = [torch.cat([base[:n], torch.randint(0, cfg["vocab_size"], (m,), generator=g)])
                for n, m in ((400, 30), (400, 70), (250, 100), (250, 9), (100, 300), (0, 120))]
-    pool = dict(max_total_tokens=2560, max_requests=4)     # C = 640; probed on the pure reference (fp32, CPU): evicts from wave 2 on, never retracts
+    # C = 640; probed on the pure reference (fp32, CPU): evicts from wave 2 on, never retracts
+    pool = dict(max_total_tokens=2560, max_requests=4)
     ref = ref_stack.build(None, cfg, "cuda", torch.bfloat16, **pool)
     got = ref_stack.build(DROPIN_DIR, cfg, "cuda", torch.bfloat16, **pool, listen=False, hooks=("prep",))
+    evictions = []
+    inner_evict = got.scheduler.tree_cache.evict
+    got.scheduler.tree_cache.evict = lambda n, cb: (evictions.append(n), inner_evict(n, cb))[1]
     for wave in range(4):      # later waves hit the tree, then outgrow it and force evictions
         g2 = torch.Generator().manual_seed(100 + wave)
         extra = [torch.cat([p[: 200 + 60 * wave], torch.randint(0, cfg["vocab_size"], (90,), generator=g2)])
                  for p in prompts[:3]]
         batch = prompts + extra if wave else prompts
         r = _run(ref, batch, "normal")
-        d = _run(got, batch, "normal")
-        _compare(f"shared-prefix/wave{wave}", r, d)
+        d = _run(got, batch, "normal", forced=[x[0] for x in r])
+        _compare_forced(f"shared-prefix/wave{wave}", r, d)
+    assert evictions, "the scenario was meant to evict"
