@@ -527,13 +527,17 @@ extern "C" int bsgl_extend_attention(const void* q, const void* k_slab, const vo
                    ((uintptr_t)out % 16 == 0),
                "bsgl_extend_attention: pointers must be 16-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
-  static const int expmode = [] {
-    const char* e = getenv("BSGL_EXT_EXPMODE");   // development knob; default = measured best (1)
-    return e ? atoi(e) : 1;
-  }();
 #define BSGL_EXT1(T, D, M)                                                                                          \
   return launch_extend<T, D, M>(q, k_slab, v_slab, req_to_token, page_table_stride, req_pool_indices, prefix_lens, \
                                 qo_indptr, req_order, batch, n_tokens, n_q_heads, n_kv_heads, sm_scale, out, s)
+#ifdef BSGL_EXT_EXPERIMENTS
+  // scripts/ builds only (-DBSGL_EXT_EXPERIMENTS): the other exponential splits and the timing experiments that
+  // skip the exponentials (4, 6) or the K/V gather (5, 6) -- the latter give WRONG results by design, which is why
+  // none of this is compiled into the shipped library.
+  static const int expmode = [] {
+    const char* e = getenv("BSGL_EXT_EXPMODE");
+    return e ? atoi(e) : 1;
+  }();
 #define BSGL_EXT(T, D)                    \
   do {                                    \
     if (expmode == 0) BSGL_EXT1(T, D, 0); \
@@ -544,6 +548,10 @@ extern "C" int bsgl_extend_attention(const void* q, const void* k_slab, const vo
     if (expmode == 6) BSGL_EXT1(T, D, 6); \
     BSGL_EXT1(T, D, 1);                   \
   } while (0)
+#else
+  // EXPMODE 1 (one exponential pair in four on the FMA pipe) is the measured best and the only one shipped
+#define BSGL_EXT(T, D) BSGL_EXT1(T, D, 1)
+#endif
   if (dtype == BSGL_BF16) {
     if (head_dim == 128) BSGL_EXT(__nv_bfloat16, 128);
     BSGL_EXT(__nv_bfloat16, 64);

@@ -18,13 +18,29 @@
 //            done-flag on every rank.
 //   phase 3  CTA 0 waits until every tile of the local output has been delivered.
 //
-// The transfer of tile i overlaps the MMAs of tile i+1 (TMEM double buffer) and the whole exchange overlaps
-// the GEMM tail; no NCCL call, no separate reduction pass over HBM.  Flags carry the call's epoch (monotonic),
-// staging and output buffers alternate with the epoch's parity: a rank can run at most one call ahead of its
-// peers (it cannot finish call n before every owner delivered call n), so two copies suffice.
+// Two exchange paths, chosen by the communicator:
+//   * NVLS (multicast mapping of the communicator buffers through the NVSwitch): phase 1 keeps each partial tile
+//     in the rank's OWN staging (no wire traffic) and only raises a flag at the owner; the owner then reads the
+//     tile with `multimem.ld_reduce` -- the switch sums the `world` copies in fp32 on the way -- and broadcasts
+//     the result with `multimem.st`.  Per rank and direction that is ~T x hidden x 2 B on the wire (10.5 MB at
+//     C5) instead of 2 (t-1)/t x that twice over (18.4 MB): one-shot instead of two-shot.  All ranks visit the
+//     tiles in the same order, so a tile completes everywhere at about the same time and the reduction trails
+//     the GEMM by a tile.
+//   * peer stores (no multicast support): phases 1/2 as written above, two-shot.
 //
-// Bound: NVLink/NVSwitch bandwidth.  Bytes on the wire per rank = 2 (t-1)/t x T x hidden x 2 B.
+// The transfer of tile i overlaps the MMAs of tile i+1 (TMEM double buffer) and the whole exchange overlaps
+// the GEMM tail; no NCCL call, no separate reduction pass over HBM.  Flags carry the call's epoch, a counter in
+// DEVICE memory that the last CTA of every launch advances (so a CUDA-graph replay numbers its calls like eager
+// launches do; every rank makes the same sequence of calls).  Buffers are single: a rank cannot finish call n
+// before every owner has read all of call n's partials and delivered all of its tiles, and the consumer of call
+// n's output is stream-ordered before the rank's own contribution to call n+1, which every write of call n+1
+// into this rank's buffers depends on.
+//
+// Bound: NVLink/NVSwitch bandwidth.
 #include <cuda.h>
+
+#include <mutex>
+#include <unordered_map>
 
 #include "tcgen05.cuh"
 
@@ -39,9 +55,11 @@ constexpr int kOpMaxWorld = 8;
 constexpr int kOpSmemBytes = kOpStages * kOpStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
 
 struct OprojComm {
-  uint8_t* staging[kOpMaxWorld];    // per rank: [2][world][max_slots] partial tiles (chunk-major 16-byte layout)
-  uint8_t* out[kOpMaxWorld];        // per rank: [2][max_tokens * hidden] bf16
-  uint32_t* flags[kOpMaxWorld];     // per rank: arrive[max_slots][8] then done[max_tiles]
+  uint8_t* staging[kOpMaxWorld];    // per rank: [world * max_slots] partial tiles (chunk-major 16-byte layout)
+  uint8_t* out[kOpMaxWorld];        // per rank: [max_tokens * hidden] bf16
+  uint32_t* flags[kOpMaxWorld];     // per rank: arrive[max_slots][8], done[max_tiles], then {epoch, finished CTAs}
+  uint8_t* mc_staging;              // multicast (NVLS) views of the same two regions; nullptr = peer-store path
+  uint8_t* mc_out;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -57,15 +75,34 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-// Spin until *p >= want (epochs are monotonic).  A peer that never shows up traps this rank after ~4 s
-// instead of hanging the GPU.
-__device__ __forceinline__ void wait_flag_ge(const uint32_t* p, uint32_t want) {
+// Spin until *p >= want (epochs are monotonic).  A peer that never shows up traps this rank after `timeout_ns`
+// (communicator setting, default 30 s: first-call lazy peer mapping, a host-side hiccup on one rank or a profiler
+// can delay a peer by seconds) instead of hanging the GPU.
+__device__ __forceinline__ void wait_flag_ge(const uint32_t* p, uint32_t want, uint64_t timeout_ns) {
   if (ld_acquire_sys(p) >= want) return;
   const uint64_t t0 = globaltimer_ns();
   while (ld_acquire_sys(p) < want) {
     __nanosleep(64);
-    if (globaltimer_ns() - t0 > 4000000000ull) __trap();
+    if (globaltimer_ns() - t0 > timeout_ns) __trap();
   }
+}
+
+// NVLS: one 16-byte load that returns the element-wise SUM over every rank's copy (fp32 accumulation inside the
+// switch), and one 16-byte store replicated into every rank's copy.
+template <typename T>
+__device__ __forceinline__ uint4 multimem_ld_reduce_add(const void* mc_ptr) {
+  uint4 r;
+  if constexpr (std::is_same<T, __nv_bfloat16>::value)
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc_ptr) : "memory");
+  else
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc_ptr) : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st(void* mc_ptr, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc_ptr), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w) : "memory");
 }
 
 __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap* tmap, int c0, int c1, uint32_t bar) {
@@ -151,18 +188,41 @@ __device__ __forceinline__ void reduce_owned_tile(const OprojComm& comm, const u
   }
 }
 
+// Phase-2 worker, NVLS path: the switch sums the `world` copies of the owned tile on the way in and replicates the
+// result on the way out.  16 independent 16-byte reductions per thread are issued before the first store.
+template <typename T>
+__device__ __forceinline__ void reduce_owned_tile_nvls(const OprojComm& comm, int tile, int etid, int m0, int n0,
+                                                       int M, int N) {
+  const uint4* src = reinterpret_cast<const uint4*>(comm.mc_staging + (int64_t)tile * kOpTileBytes);
+  uint4 v[16];
+#pragma unroll
+  for (int u = 0; u < 16; ++u) {
+    const int item = u * 128 + etid;
+    const int c = item & 15, r = item >> 4;
+    v[u] = multimem_ld_reduce_add<T>(src + c * 128 + r);
+  }
+#pragma unroll
+  for (int u = 0; u < 16; ++u) {
+    const int item = u * 128 + etid;
+    const int c = item & 15, r = item >> 4;
+    if (m0 + r < M) multimem_st(comm.mc_out + ((int64_t)(m0 + r) * N + n0 + c * 8) * 2, v[u]);
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kOpThreads, 1)
 oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                        const __grid_constant__ OprojComm comm, int M, int N, int K, int rank, int world, int max_slots,
-                       int64_t out_parity_bytes, uint32_t epoch) {
+                       int max_tiles, uint64_t timeout_ns) {
   extern __shared__ uint8_t smem_dyn[];
   const uint32_t raw = smem_u32(smem_dyn);
   const uint32_t base = (raw + 1023u) & ~1023u;          // SWIZZLE_128B tiles need 1024-byte alignment
   uint8_t* smem = smem_dyn + (base - raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_nt = N / kOpBN, n_mt = (M + kOpBM - 1) / kOpBM, n_tiles = n_mt * n_nt, n_kb = K / kOpBK;
-  const uint32_t par = epoch & 1u;
+  const bool nvls = comm.mc_staging != nullptr;
+  uint32_t* ctl = comm.flags[rank] + max_slots * kOpMaxWorld + max_tiles;   // {epoch of the last finished call, CTAs done}
+  const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(ctl) + 1u;   // advanced by the last CTA of each launch
 
   const uint32_t bar0 = base + kOpStages * kOpStageBytes;
   const uint32_t full0 = bar0, empty0 = bar0 + 8 * kOpStages, accf0 = empty0 + 8 * kOpStages, acce0 = accf0 + 16;
@@ -194,7 +254,7 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
       tma_prefetch_desc(&tm_b);
       uint32_t it = 0;
       for (int i = blockIdx.x; i < n_tiles; i += gridDim.x) {
-        const int tile = tile_at(i, n_tiles, rank, world);
+        const int tile = nvls ? i : tile_at(i, n_tiles, rank, world);
         const int m0 = (tile / n_nt) * kOpBM, n0 = (tile % n_nt) * kOpBN;
         for (int kb = 0; kb < n_kb; ++kb, ++it) {
           const uint32_t s = it % kOpStages, ph = (it / kOpStages) & 1u;
@@ -238,7 +298,7 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     uint32_t tcount = 0;
     for (int i = blockIdx.x; i < n_tiles; i += gridDim.x, ++tcount) {
-      const int tile = tile_at(i, n_tiles, rank, world);
+      const int tile = nvls ? i : tile_at(i, n_tiles, rank, world);
       const int owner = tile % world, slot = tile / world;
       const uint32_t buf = tcount & 1u;
       mbar_wait_guarded(accf0 + 8 * buf, (tcount >> 1) & 1u);
@@ -250,8 +310,11 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
       tc::fence_before_sync();
       mbar_arrive(acce0 + 8 * buf);                           // the MMA warp may start the tile after next
       // staging layout: 16-byte chunk c of row r at (c * 128 + r) * 16 -> a warp store is one 512-byte burst
-      uint4* dst = reinterpret_cast<uint4*>(comm.staging[owner] +
-                                            ((int64_t)(par * world + rank) * max_slots + slot) * kOpTileBytes);
+      // NVLS: the partial stays in this rank's own staging (the owner's multimem.ld_reduce pulls it through the
+      // switch); peer-store path: straight into the owner's staging over NVLink
+      uint4* dst = reinterpret_cast<uint4*>(
+          nvls ? comm.staging[rank] + (int64_t)tile * kOpTileBytes
+               : comm.staging[owner] + ((int64_t)rank * max_slots + slot) * kOpTileBytes);
 #pragma unroll
       for (int c = 0; c < 16; ++c) {
         const uint32_t* v = &acc[c >> 2][(c & 3) * 8];
@@ -270,7 +333,7 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
     if (blockIdx.x == 0) {
       const uint32_t* my_flags = comm.flags[rank];
       const int done_off = max_slots * kOpMaxWorld;
-      for (int tile = etid; tile < n_tiles; tile += 128) wait_flag_ge(my_flags + done_off + tile, epoch);
+      for (int tile = etid; tile < n_tiles; tile += 128) wait_flag_ge(my_flags + done_off + tile, epoch, timeout_ns);
     }
   } else {
     // ======================================================== owner reduce (phase 2), concurrent with phase 1:
@@ -283,12 +346,14 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
     for (int j = blockIdx.x; j < n_owned; j += gridDim.x) {
       const int tile = rank + world * j;
       const int m0 = (tile / n_nt) * kOpBM, n0 = (tile % n_nt) * kOpBN;
-      if (etid < world) wait_flag_ge(my_flags + j * kOpMaxWorld + etid, epoch);
+      if (etid < world) wait_flag_ge(my_flags + j * kOpMaxWorld + etid, epoch, timeout_ns);
       named_bar_sync(2, 128);
-      const uint8_t* part0 = comm.staging[rank] + ((int64_t)par * world * max_slots + j) * kOpTileBytes;
+      const uint8_t* part0 = comm.staging[rank] + (int64_t)j * kOpTileBytes;
       const int64_t src_stride = (int64_t)max_slots * kOpTileBytes;
-      const int64_t out_base = (int64_t)par * out_parity_bytes;
-      if (world <= 2)
+      const int64_t out_base = 0;
+      if (nvls)
+        reduce_owned_tile_nvls<T>(comm, tile, etid, m0, n0, M, N);
+      else if (world <= 2)
         reduce_owned_tile<T, 2>(comm, part0, src_stride, world, etid, m0, n0, M, N, out_base);
       else if (world <= 4)
         reduce_owned_tile<T, 4>(comm, part0, src_stride, world, etid, m0, n0, M, N, out_base);
@@ -304,6 +369,15 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
   if (warp == 1) {
     tc::fence_after_sync();
     tc::tmem_dealloc(tmem, 256);
+  }
+  // the last CTA to get here closes the call: every CTA has read `epoch` by now, none will read it again
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(ctl + 1, 1u) == gridDim.x - 1) {
+      ctl[1] = 0u;
+      *reinterpret_cast<volatile uint32_t*>(ctl) = epoch;
+      __threadfence();
+    }
   }
 }
 
@@ -329,7 +403,36 @@ static EncodeTiledFn encode_tiled_fn() {
 }
 
 // [rows, K] row-major 16-bit matrix, rows `ld` elements apart -> 2-D map with a {64 x 128} box, 128B swizzle.
+// Encoding is a driver call (~1-2 us); the weight's map never changes and the activation buffer of a layer is
+// usually the same allocation step after step, so maps are cached by (pointer, shape, pitch, dtype).
+struct MapKey {
+  const void* ptr;
+  int64_t rows, K, ld;
+  int dtype;
+  bool operator==(const MapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && K == o.K && ld == o.ld && dtype == o.dtype;
+  }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    size_t h = std::hash<const void*>()(k.ptr);
+    for (int64_t v : {k.rows, k.K, k.ld, (int64_t)k.dtype}) h = h * 1315423911u + std::hash<int64_t>()(v);
+    return h;
+  }
+};
+
 static int make_map(CUtensorMap* m, const void* ptr, int64_t rows, int64_t K, int64_t ld, int dtype) {
+  static std::mutex mu;
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  const MapKey key{ptr, rows, K, ld, dtype};
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+      *m = it->second;
+      return BSGL_OK;
+    }
+  }
   EncodeTiledFn fn = encode_tiled_fn();
   BSGL_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
   const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
@@ -340,13 +443,15 @@ static int make_map(CUtensorMap* m, const void* ptr, int64_t rows, int64_t K, in
                   const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   BSGL_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  std::lock_guard<std::mutex> lock(mu);
+  if (cache.size() >= 1024) cache.clear();
+  cache.emplace(key, *m);
   return BSGL_OK;
 }
 
 template <typename T>
 static int launch_oproj(const CUtensorMap& ta, const CUtensorMap& tb, const OprojComm& comm, int M, int N, int K,
-                        int rank, int world, int max_slots, int64_t out_parity_bytes, uint32_t epoch,
-                        cudaStream_t stream) {
+                        int rank, int world, int max_slots, int max_tiles, uint64_t timeout_ns, cudaStream_t stream) {
   auto kern = oproj_allreduce_kernel<T>;
   static thread_local int configured_dev = -1;
   int dev = 0, sms = 0;
@@ -357,10 +462,11 @@ static int launch_oproj(const CUtensorMap& ta, const CUtensorMap& tb, const Opro
   }
   BSGL_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int n_tiles = ((M + kOpBM - 1) / kOpBM) * (N / kOpBN);
-  // every CTA must be resident: phase 2 waits on tiles other CTAs of this grid produce
+  // every CTA must be resident: phase 2 waits on tiles other CTAs of this grid produce (one CTA per SM: 197 KB of
+  // shared memory each; a persistent kernel of another stream holding SMs would stall it until the timeout)
   const int grid = n_tiles < sms ? n_tiles : sms;
-  kern<<<grid, kOpThreads, kOpSmemBytes, stream>>>(ta, tb, comm, M, N, K, rank, world, max_slots, out_parity_bytes,
-                                                   epoch);
+  kern<<<grid, kOpThreads, kOpSmemBytes, stream>>>(ta, tb, comm, M, N, K, rank, world, max_slots, max_tiles,
+                                                   timeout_ns);
   return check_launch("oproj_allreduce_kernel");
 }
 
@@ -404,8 +510,9 @@ extern "C" int bsgl_comm_free(void* dev_ptr) {
 
 extern "C" int bsgl_oproj_allreduce(const void* a, int64_t lda, const void* w, int64_t ldw, int n_tokens, int hidden,
                                     int k_local, int rank, int world, void* const* staging_ptrs,
-                                    void* const* out_ptrs, void* const* flag_ptrs, int max_slots, int max_tiles,
-                                    int64_t out_parity_bytes, uint32_t epoch, int dtype, void* stream) {
+                                    void* const* out_ptrs, void* const* flag_ptrs, void* mc_staging, void* mc_out,
+                                    int max_slots, int max_tiles, int64_t out_bytes, double timeout_s, int dtype,
+                                    void* stream) {
   using namespace bsgl;
   BSGL_REQUIRE(n_tokens >= 0, "bsgl_oproj_allreduce: negative token count");
   BSGL_REQUIRE(a && w && staging_ptrs && out_ptrs && flag_ptrs, "bsgl_oproj_allreduce: null pointer");
@@ -419,13 +526,15 @@ extern "C" int bsgl_oproj_allreduce(const void* a, int64_t lda, const void* w, i
   BSGL_REQUIRE(lda >= k_local && ldw >= k_local && lda % 8 == 0 && ldw % 8 == 0 && (uintptr_t)a % 16 == 0 &&
                    (uintptr_t)w % 16 == 0,
                "bsgl_oproj_allreduce: operands must be 16-byte aligned with row strides that are multiples of 8");
-  BSGL_REQUIRE(epoch > 0, "bsgl_oproj_allreduce: epoch starts at 1 (flags are zero-initialised)");
+  BSGL_REQUIRE((mc_staging == nullptr) == (mc_out == nullptr),
+               "bsgl_oproj_allreduce: the multicast views of staging and output go together");
+  BSGL_REQUIRE(timeout_s > 0.0, "bsgl_oproj_allreduce: timeout must be positive");
   if (n_tokens == 0) return BSGL_OK;
   const int n_tiles = ((n_tokens + kOpBM - 1) / kOpBM) * (hidden / kOpBN);
   BSGL_REQUIRE(n_tiles <= max_tiles && (n_tiles + world - 1) / world <= max_slots,
                "bsgl_oproj_allreduce: %d tiles exceed the communicator (max_tiles %d, max_slots %d)", n_tiles,
                max_tiles, max_slots);
-  BSGL_REQUIRE((int64_t)n_tokens * hidden * 2 <= out_parity_bytes, "bsgl_oproj_allreduce: output buffer too small");
+  BSGL_REQUIRE((int64_t)n_tokens * hidden * 2 <= out_bytes, "bsgl_oproj_allreduce: output buffer too small");
   OprojComm comm;
   for (int i = 0; i < kOpMaxWorld; ++i) {
     const int j = i < world ? i : 0;
@@ -434,15 +543,18 @@ extern "C" int bsgl_oproj_allreduce(const void* a, int64_t lda, const void* w, i
     comm.out[i] = (uint8_t*)out_ptrs[j];
     comm.flags[i] = (uint32_t*)flag_ptrs[j];
   }
+  comm.mc_staging = (uint8_t*)mc_staging;
+  comm.mc_out = (uint8_t*)mc_out;
   CUtensorMap ta, tb;
   int rc = make_map(&ta, a, n_tokens, k_local, lda, dtype);
   if (rc != BSGL_OK) return rc;
   rc = make_map(&tb, w, hidden, k_local, ldw, dtype);
   if (rc != BSGL_OK) return rc;
   cudaStream_t s = (cudaStream_t)stream;
+  const uint64_t timeout_ns = (uint64_t)(timeout_s * 1e9);
   if (dtype == BSGL_BF16)
-    return launch_oproj<__nv_bfloat16>(ta, tb, comm, n_tokens, hidden, k_local, rank, world, max_slots,
-                                       out_parity_bytes, epoch, s);
-  return launch_oproj<__half>(ta, tb, comm, n_tokens, hidden, k_local, rank, world, max_slots, out_parity_bytes, epoch,
+    return launch_oproj<__nv_bfloat16>(ta, tb, comm, n_tokens, hidden, k_local, rank, world, max_slots, max_tiles,
+                                       timeout_ns, s);
+  return launch_oproj<__half>(ta, tb, comm, n_tokens, hidden, k_local, rank, world, max_slots, max_tiles, timeout_ns,
                               s);
 }

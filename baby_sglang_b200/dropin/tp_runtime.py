@@ -120,21 +120,39 @@ def _attention_modules(model: torch.nn.Module):
             yield m
 
 
-class FusedOProjAllReduce:
-    """`o_proj` + SUM all-reduce as ONE kernel per rank over NVLink peer memory (K8, `bsgl_oproj_allreduce`),
-    in place of `F.linear` + `dist.all_reduce` (qwen2.py:195 + tp_runtime.py:28-33).
+class _RawView:
+    """Zero-copy torch view of raw device memory (via __cuda_array_interface__)."""
 
-    One communicator serves every layer: a staging area for partial tiles, two output buffers and the
-    flags, allocated once through the C ABI (cudaMalloc + CUDA IPC), exported to the peers with
-    `dist.all_gather_object` and mapped here.  Calls are numbered (`epoch`); every rank must make the same
-    sequence of calls, which the replicated scheduler guarantees.  The returned tensor is a view of this rank's
-    output buffer of the call's parity: it stays valid until the call after next (the reference's layer consumes
-    it at once: residual add + RMSNorm create new tensors, qwen2.py:113-121)."""
+    @staticmethod
+    def make(ptr: int, shape, dtype: torch.dtype, device) -> torch.Tensor:
+        typestr = {torch.bfloat16: "<u2", torch.float16: "<f2", torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
+        holder = type("_CAI", (), {})()
+        holder.__cuda_array_interface__ = {"shape": tuple(int(x) for x in shape), "typestr": typestr,
+                                           "data": (int(ptr), False), "version": 3}
+        t = torch.as_tensor(holder, device=device)
+        return t.view(dtype) if t.dtype != dtype else t
+
+
+class FusedOProjAllReduce:
+    """`o_proj` + SUM all-reduce as ONE kernel per rank over NVLink (K8, `bsgl_oproj_allreduce`), in place of
+    `F.linear` + `dist.all_reduce` (qwen2.py:195 + tp_runtime.py:28-33).
+
+    One communicator serves every layer: a staging area for partial tiles, an output buffer and the flags.
+    The memory comes from torch's symmetric-memory allocator when it is available (plumbing only: allocation,
+    peer mapping and the NVSwitch MULTICAST mapping; `exchange = "nvls"`): partial tiles then stay in each rank's
+    own staging and the tile's owner reduces them inside the switch (`multimem.ld_reduce`) and broadcasts the sum
+    (`multimem.st`).  Without multicast support the buffers are cudaMalloc + CUDA IPC through the C ABI and
+    partial tiles travel by peer stores (`exchange = "peer-stores"`).  `BSGL_K8_EXCHANGE=peer` forces the latter.
+
+    Every rank must make the same sequence of calls, which the replicated scheduler guarantees; the call counter
+    lives in device memory, so the call can sit inside a captured CUDA graph.  The returned tensor is a view of
+    this rank's output buffer: valid until this communicator's next call (the reference's layer consumes it at
+    once: residual add + RMSNorm create new tensors, qwen2.py:113-121)."""
 
     TILE = 128
 
     def __init__(self, rank: int, world_size: int, tp_group, hidden: int, max_tokens: int,
-                 dtype: torch.dtype = torch.bfloat16, device=None):
+                 dtype: torch.dtype = torch.bfloat16, device=None, timeout_s: float = None):
         from baby_sglang_b200 import ops
         if hidden % self.TILE:
             raise ValueError(f"hidden {hidden} is not a multiple of {self.TILE}")
@@ -143,34 +161,85 @@ class FusedOProjAllReduce:
         self._ops, self.rank, self.world, self.group = ops, rank, world_size, tp_group
         self.hidden, self.max_tokens, self.dtype = hidden, max_tokens, dtype
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.timeout_s = float(os.environ.get("BSGL_K8_TIMEOUT_S", "30")) if timeout_s is None else float(timeout_s)
         self.max_tiles = -(-max_tokens // self.TILE) * (hidden // self.TILE)
         self.max_slots = -(-self.max_tiles // world_size)
         up = lambda n: -(-n // 1024) * 1024
-        self.out_parity_bytes = up(max_tokens * hidden * 2)
-        staging_bytes = 2 * world_size * self.max_slots * self.TILE * self.TILE * 2
+        self.out_bytes = up(max_tokens * hidden * 2)
+        staging_bytes = world_size * self.max_slots * self.TILE * self.TILE * 2
         self._off_out = up(staging_bytes)
-        self._off_flags = self._off_out + 2 * self.out_parity_bytes
-        self.nbytes = self._off_flags + up((self.max_slots * 8 + self.max_tiles) * 4)
-        self._mine = ops.CommBuffer.alloc(self.nbytes)
-        self._peers = [None] * world_size
-        if world_size > 1:
-            handles = [None] * world_size
-            dist.all_gather_object(handles, self._mine.handle, group=tp_group)
-            for r, h in enumerate(handles):
-                self._peers[r] = self._mine if r == rank else ops.CommBuffer.open(h, self.nbytes)
-            dist.barrier(group=tp_group)
-        else:
-            self._peers[0] = self._mine
-        base = [b.ptr for b in self._peers]
+        self._off_flags = self._off_out + self.out_bytes
+        self.nbytes = self._off_flags + up((self.max_slots * 8 + self.max_tiles + 2) * 4)
+        self._mine = None
+        self._peers = []
+        self._symm = None
+        mc = 0
+        base = None
+        if world_size > 1 and os.environ.get("BSGL_K8_EXCHANGE", "") != "peer":
+            base, mc = self._alloc_symmetric()
+        if base is None:
+            base = self._alloc_ipc()
+        self.exchange = "nvls (multimem.ld_reduce / multimem.st over the NVSwitch multicast mapping)" if mc else \
+            ("peer-stores (two-shot over NVLink peer memory)" if world_size > 1 else "local (world 1)")
         self._staging = base
         self._out = [p + self._off_out for p in base]
         self._flags = [p + self._off_flags for p in base]
-        # built once: the pointer tables the C ABI takes and the two output views (as_tensor costs tens of µs)
+        self._mc_staging = mc if mc else 0
+        self._mc_out = mc + self._off_out if mc else 0
+        # built once: the pointer tables the C ABI takes and the output view (as_tensor costs tens of us)
         self._ptr_tables = ops.oproj_pointer_tables(self._staging, self._out, self._flags)
-        self._out_views = [self._mine.as_tensor(self._off_out + par * self.out_parity_bytes,
-                                                (max_tokens, hidden), dtype, self.device) for par in (0, 1)]
-        self.epoch = 0
+        self._out_view = _RawView.make(base[rank] + self._off_out, (max_tokens, hidden), dtype, self.device)
+        self.calls = 0
+        # handshake: one tiny call absorbs the lazy peer mapping / module load on every rank before timing matters
+        if world_size > 1:
+            a0 = torch.zeros(1, 64, dtype=dtype, device=self.device)
+            w0 = torch.zeros(hidden, 64, dtype=dtype, device=self.device)
+            self(a0, w0)
+            torch.cuda.synchronize()
+            dist.barrier(group=tp_group)
 
+    # -- memory ------------------------------------------------------------------------------------------
+    def _alloc_symmetric(self):
+        """torch symmetric memory: same-size buffer on every rank, peer-mapped, plus the multicast mapping."""
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            t = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+            t.zero_()
+            torch.cuda.synchronize()
+            hdl = symm_mem.rendezvous(t, self.group)
+            base = [int(p) for p in hdl.buffer_ptrs]
+            mc = int(hdl.multicast_ptr) if getattr(hdl, "has_multicast_support", False) else 0
+            if len(base) != self.world or base[self.rank] != t.data_ptr():
+                raise RuntimeError("unexpected symmetric-memory pointer table")
+            flag = torch.tensor([1 if mc else 0], device=self.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)     # all ranks or none
+            mc = mc if int(flag.item()) else 0
+            self._symm = (t, hdl)
+            return base, mc
+        except Exception as e:   # older torch / no fabric: fall back to cudaMalloc + IPC
+            self._symm_error = repr(e)
+            ok = torch.tensor([0], device=self.device)
+            try:
+                dist.all_reduce(ok, group=self.group)
+            except Exception:
+                pass
+            return None, 0
+
+    def _alloc_ipc(self):
+        ops = self._ops
+        self._mine = ops.CommBuffer.alloc(self.nbytes)
+        self._peers = [None] * self.world
+        if self.world > 1:
+            handles = [None] * self.world
+            dist.all_gather_object(handles, self._mine.handle, group=self.group)
+            for r, h in enumerate(handles):
+                self._peers[r] = self._mine if r == self.rank else ops.CommBuffer.open(h, self.nbytes)
+            dist.barrier(group=self.group)
+        else:
+            self._peers[0] = self._mine
+        return [b.ptr for b in self._peers]
+
+    # -- the call ----------------------------------------------------------------------------------------
     def __call__(self, attn_out: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
         """attn_out [T, K_r] (this rank's heads), weight [hidden, K_r] (this rank's o_proj columns) ->
         the all-reduced [T, hidden], bit-identical on every rank."""
@@ -179,10 +248,10 @@ class FusedOProjAllReduce:
             raise ValueError(f"{T} tokens exceed the communicator's max_tokens {self.max_tokens}")
         if attn_out.dtype != self.dtype or weight.dtype != self.dtype or int(weight.shape[0]) != self.hidden:
             raise ValueError("dtype / hidden size differ from the communicator's")
-        self.epoch += 1
-        self._ops.oproj_allreduce(attn_out, weight, self.rank, self.world, *self._ptr_tables,
-                                  self.max_slots, self.max_tiles, self.out_parity_bytes, self.epoch)
-        return self._out_views[self.epoch & 1][:T]
+        self.calls += 1
+        self._ops.oproj_allreduce(attn_out, weight, self.rank, self.world, *self._ptr_tables, self.max_slots,
+                                  self.max_tiles, self.out_bytes, self._mc_staging, self._mc_out, self.timeout_s)
+        return self._out_view[:T]
 
     def close(self) -> None:
         if self.world > 1 and dist.is_initialized():
@@ -191,8 +260,9 @@ class FusedOProjAllReduce:
         for r, b in enumerate(self._peers):
             if b is not None and r != self.rank:
                 b.release()
-        self._mine.release()
-        self._peers = []
+        if self._mine is not None:
+            self._mine.release()
+        self._peers, self._mine, self._symm = [], None, None
 
 
 def shard_attention_heads(model: torch.nn.Module, rank: int, world_size: int, tp_group,

@@ -588,10 +588,13 @@ def oproj_pointer_tables(staging_ptrs, out_ptrs, flag_ptrs):
 
 
 def oproj_allreduce(a: torch.Tensor, w: torch.Tensor, rank: int, world: int, staging_ptrs, out_ptrs, flag_ptrs,
-                    max_slots: int, max_tiles: int, out_parity_bytes: int, epoch: int) -> None:
+                    max_slots: int, max_tiles: int, out_bytes: int, mc_staging: int = 0, mc_out: int = 0,
+                    timeout_s: float = 30.0) -> None:
     """K8 launch: this rank's o_proj partial GEMM with the SUM all-reduce fused in (reference qwen2.py:195 +
     tp_runtime.py:28-33).  `a` [T, K_r] and `w` [hidden, K_r] are this rank's shard; the result lands in every
-    rank's output buffer at parity `epoch & 1`.  All ranks must call with the same epoch."""
+    rank's output buffer.  `mc_staging` / `mc_out` are the NVLS multicast views of the staging / output regions
+    (0 = exchange by peer stores).  All ranks must make the same sequence of calls (the call counter lives in
+    device memory, so the launch can be captured into a CUDA graph)."""
     _require_cuda(a, w)
     if a.dtype != w.dtype or a.dim() != 2 or w.dim() != 2 or a.shape[1] != w.shape[1]:
         raise _lib.BsglError(f"oproj_allreduce: a {tuple(a.shape)} {a.dtype} vs w {tuple(w.shape)} {w.dtype}")
@@ -601,7 +604,8 @@ def oproj_allreduce(a: torch.Tensor, w: torch.Tensor, rank: int, world: int, sta
         staging_ptrs, out_ptrs, flag_ptrs = oproj_pointer_tables(staging_ptrs, out_ptrs, flag_ptrs)
     rc = _lib.load().bsgl_oproj_allreduce(
         a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), int(a.shape[0]), int(w.shape[0]), int(a.shape[1]),
-        int(rank), int(world), staging_ptrs, out_ptrs, flag_ptrs, int(max_slots), int(max_tiles),
-        int(out_parity_bytes), int(epoch), dtype_code(a.dtype), _stream())
+        int(rank), int(world), staging_ptrs, out_ptrs, flag_ptrs, ctypes.c_void_p(int(mc_staging) or None),
+        ctypes.c_void_p(int(mc_out) or None), int(max_slots), int(max_tiles), int(out_bytes), float(timeout_s),
+        dtype_code(a.dtype), _stream())
     _lib.check(rc, "bsgl_oproj_allreduce")
     _count()

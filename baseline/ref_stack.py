@@ -170,6 +170,7 @@ class StackRun:
     model: object
     log: SampleLog
     tracker: Optional[StepTracker] = None
+    comm: object = None            # FusedOProjAllReduce of a TP-sharded stack (close() it collectively)
 
     def state(self) -> Dict[str, object]:
         """The index state the north star requires to be bit-exact."""
@@ -184,10 +185,13 @@ class StackRun:
 
 
 def build(shadow_dir: Optional[str], cfg_kwargs: dict, device: str, dtype: torch.dtype, max_total_tokens: int,
-          max_requests: int, hooks: Sequence[str] = (), listen: bool = True, init: str = "deterministic") -> StackRun:
+          max_requests: int, hooks: Sequence[str] = (), listen: bool = True, init: str = "deterministic",
+          tp: Optional[dict] = None) -> StackRun:
     """Reference scheduler + model on `device`; `shadow_dir=None` is the pure reference, `DROPIN_DIR` the product.
     `hooks` ⊆ {"rope", "sampler", "prep", "graph"} installs the row-(f) kernels (baby_sglang_b200.model_hooks) on
-    the instances."""
+    the instances.  `tp = dict(rank, world, group, fused: bool, mlp: bool)` shards the unchanged model with the
+    drop-in `tp_runtime` (KV-head TP; the scheduler's pool shrinks through `kv_pool_config`) before the scheduler
+    is built."""
     st = ref_loader.load_stack(shadow_dir=shadow_dir)
     os.environ["BABYSGL_MAX_TOTAL_TOKENS"] = str(max_total_tokens)     # scheduler.py:33-36
     os.environ["BABYSGL_MAX_REQUESTS"] = str(max_requests)
@@ -208,6 +212,18 @@ def build(shadow_dir: Optional[str], cfg_kwargs: dict, device: str, dtype: torch
         for m in model.modules():       # rotary buffers are built with explicit CPU/float math in the reference
             for name, buf in list(m.named_buffers(recurse=False)):
                 setattr(m, name, buf.to(device))
+    comm = None
+    if tp is not None:
+        tpr = st.tp_runtime
+        if tp.get("fused"):
+            comm = tpr.FusedOProjAllReduce(tp["rank"], tp["world"], tp["group"], hidden=cfg.hidden_size,
+                                           max_tokens=tp.get("max_tokens", 1024), dtype=dtype)
+        plan = tpr.shard_attention_heads(model, tp["rank"], tp["world"], tp["group"], fused_allreduce=comm)
+        if plan.mode != "kv_head_tp":
+            raise ValueError(f"geometry does not shard over {tp['world']} ranks: {plan}")
+        if tp.get("mlp"):
+            tpr.shard_mlp(model, tp["rank"], tp["world"], tp["group"])
+        model.config = tpr.kv_pool_config(model.config, plan)      # scheduler.py:50-57 reads num_key_value_heads
     sched = st.scheduler.Scheduler(model, tokenizer=None)
     log = SampleLog()
     tracker = None
@@ -224,7 +240,9 @@ def build(shadow_dir: Optional[str], cfg_kwargs: dict, device: str, dtype: torch
             model_hooks.install_device_batch_prep(sched)
         if "graph" in hooks:
             model_hooks.install_cuda_graph_decode(model)
-    return StackRun(st, sched, model, log, tracker)
+    run = StackRun(st, sched, model, log, tracker)
+    run.comm = comm
+    return run
 
 
 def classify_divergence(ref_ids: List[List[int]], got_ids: List[List[int]], ref_margins: List[List[List[float]]],
@@ -285,9 +303,10 @@ def seed_decode_state(run: StackRun, batch: int, ctx: int, max_new_tokens: int, 
     for i in range(0, batch, chunk):
         sched._prepare_prefill_batch(reqs[i:i + chunk])          # rows + slots + page-table rows; batch discarded
     pool = sched.token_to_kv_pool
+    gdev = torch.Generator(device=dev).manual_seed(seed)            # same KV contents for every stack / variant
     for l in range(pool.layer_num):
-        pool.k_buffer[l].normal_()
-        pool.v_buffer[l].normal_()
+        pool.k_buffer[l].normal_(generator=gdev)
+        pool.v_buffer[l].normal_(generator=gdev)
     first = torch.randint(0, vocab, (batch,), generator=g).tolist()
     for r, t in zip(reqs, first):
         r.output_ids.append(int(t))

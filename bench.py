@@ -535,6 +535,22 @@ def measure_decode_tok_s(device, steps=64, batch=256, ctx=4096):
     out["best_variant"] = [k for k, x in out["variants"].items() if x is best][0]
     del run, model
     _free()
+    # context only: the PURE reference stack (its own torch attention path: 28 x 256 SDPA calls and ~14 k host
+    # syncs per step) on the same GPU, same seeded state, a few steps
+    try:
+        ref = ref_stack.build(None, cfg, str(device), torch.bfloat16, **pool, listen=False, init="device")
+        ref_stack.seed_decode_state(ref, batch, ctx, 8, seed=0)
+        r = ref_stack.timed_decode_steps(ref, 3, warmup=1)
+        med = statistics.median(r["host_ms"])
+        out["pure_reference_on_this_gpu"] = {
+            "ms_per_step_median": round(med, 1), "decode_tok_per_s": round(batch / (med / 1e3), 1), "steps": 3,
+            "first_step_ids_identical_to_dropin": r["ids"][0] == ids_ref[0],
+            "note": "the reference's unmodified attn_backend/memory_pool/forward_batch (torch gathers + SDPA per "
+                    "request) under the same scheduler and model; context, not the baseline arm"}
+        del ref
+    except Exception as e:
+        out["pure_reference_on_this_gpu"] = {"error": repr(e)[:300]}
+    _free()
     return out
 
 

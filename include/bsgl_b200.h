@@ -231,20 +231,24 @@ int bsgl_slot_ring_push(int32_t* ring, int64_t capacity, int64_t tail, int64_t n
  * bsgl_oproj_allreduce: out[T, hidden] = SUM_ranks( a_r[T, K_r] . w_r[hidden, K_r]^T ), identical bits on every rank.
  *   a            [n_tokens, k_local]  this rank's attention output, rows lda elements apart (bf16/fp16)
  *   w            [hidden, k_local]    this rank's column shard of o_proj.weight, rows ldw elements apart
- *   staging_ptrs [world]  every rank's staging buffer as mapped here: 2 * world * max_slots * 32 KiB
- *   out_ptrs     [world]  every rank's output buffer: 2 * out_parity_bytes; this rank reads its own at
- *                         out_ptrs[rank] + (epoch & 1) * out_parity_bytes after the call (stream-ordered)
- *   flag_ptrs    [world]  every rank's flags: (max_slots * 8 + max_tiles) uint32, zero-initialised
- *   epoch        1, 2, 3, ... the same on every rank for the same call; all ranks must make the same calls
- * hidden % 128 == 0, k_local % 64 == 0, world <= 8.  A peer that never arrives traps the kernel after ~4 s. */
+ *   staging_ptrs [world]  every rank's staging buffer as mapped here: world * max_slots * 32 KiB
+ *   out_ptrs     [world]  every rank's output buffer (out_bytes); this rank reads its own at out_ptrs[rank]
+ *                         after the call (stream-ordered); valid until the rank's next call
+ *   flag_ptrs    [world]  every rank's flags: (max_slots * 8 + max_tiles + 2) uint32, zero-initialised; the last
+ *                         two words of a rank's own flags are the call counter (epoch) and a CTA counter, kept in
+ *                         device memory so that a captured CUDA graph numbers its calls like eager launches
+ *   mc_staging / mc_out   NVLS multicast views of the same staging / output regions (every rank's copy behind
+ *                         one address), or both NULL: then partial tiles travel by peer stores (two-shot)
+ *   timeout_s    a peer that never arrives traps the kernel after this many seconds
+ * All ranks must make the same sequence of calls.  hidden % 128 == 0, k_local % 64 == 0, world <= 8. */
 int bsgl_comm_alloc(int64_t bytes, void** dev_ptr, void* ipc_handle_64);
 int bsgl_comm_open(const void* ipc_handle_64, void** dev_ptr);
 int bsgl_comm_close(void* dev_ptr);
 int bsgl_comm_free(void* dev_ptr);
 int bsgl_oproj_allreduce(const void* a, int64_t lda, const void* w, int64_t ldw, int n_tokens, int hidden,
                          int k_local, int rank, int world, void* const* staging_ptrs,
-                         void* const* out_ptrs, void* const* flag_ptrs, int max_slots, int max_tiles,
-                         int64_t out_parity_bytes, uint32_t epoch, int dtype, void* stream);
+                         void* const* out_ptrs, void* const* flag_ptrs, void* mc_staging, void* mc_out,
+                         int max_slots, int max_tiles, int64_t out_bytes, double timeout_s, int dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -41,8 +41,25 @@ def main():
         g = torch.Generator(device="cpu").manual_seed(1000 * T + rank)
         a = torch.randn(T, K, generator=g).to(dev, torch.bfloat16)
         w = (torch.randn(hidden, K, generator=g) * 0.05).to(dev, torch.bfloat16)
-        for rep in range(3):                      # consecutive calls exercise both parities and epoch hand-over
+        for rep in range(3):                      # consecutive calls exercise the epoch hand-over
             out = comm(a, w).clone()
+        # the same call captured into a CUDA graph and replayed: the call counter lives in device memory, so every
+        # replay is a new epoch on every rank (a host-side epoch would have been baked into the graph)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            comm(a, w)
+        torch.cuda.current_stream().wait_stream(side)
+        with torch.cuda.graph(graph):
+            g_out = comm(a, w).clone()
+        replay_same = True
+        for rep in range(3):
+            g_out.zero_()
+            graph.replay()
+            torch.cuda.synchronize()
+            replay_same &= bool(torch.equal(g_out, out))
+        del graph
         # the pair it replaces
         ref = torch.nn.functional.linear(a, w)
         dist.all_reduce(ref, group=group)
@@ -56,9 +73,10 @@ def main():
         err_nccl = (out.float() - ref.float()).abs().max().item()
         scale = exact.abs().max().item()
         tol = 2.0 ** -7 * scale * (1 + world / 4)        # each partial is rounded to bf16 once, the sum once more
-        good = same and err_exact <= tol and err_nccl <= 2 * tol
+        good = same and replay_same and err_exact <= tol and err_nccl <= 2 * tol
         ok &= good
         line = {"case": f"T={T} hidden={hidden} K/rank={K}", "world": world, "bit_identical_across_ranks": same,
+                "cuda_graph_replays_identical": replay_same, "exchange": comm.exchange,
                 "max_abs_err_vs_fp32": err_exact, "max_abs_err_vs_nccl_pair": err_nccl, "tol": tol, "ok": good}
         if bench and T == 1024:
             def timed(fn, n=50):
