@@ -45,7 +45,8 @@ __device__ __forceinline__ unsigned long long pack(unsigned hi, unsigned lo) {
   return ((unsigned long long)hi << 32) | lo;
 }
 
-// Writes plan_hdr and cta_first_seq once tile_indptr[0..n_seqs] is complete (caller synced).
+// Writes plan_hdr and cta_first_seq (2 * (n_ctas + 1) ints: the table, then zeroed merge counters) once
+// tile_indptr[0..n_seqs] is complete (caller synced).
 __device__ void finish_plan(int n_tiles, int n_seqs, int n_ctas, int32_t* plan_hdr, const int32_t* tile_indptr,
                             int32_t* cta_first_seq) {
   int n_eff = n_tiles / BSGL_MIN_TILES_PER_CTA;
@@ -70,6 +71,9 @@ __device__ void finish_plan(int n_tiles, int n_seqs, int n_ctas, int32_t* plan_h
       j = lo;
     }
     cta_first_seq[c] = j;
+    // second half of the buffer: the fused merge's per-sequence arrival counters (paged_attention.cu), zeroed
+    // here once per batch; their last user of every launch resets them
+    cta_first_seq[n_ctas + 1 + c] = 0;
   }
 }
 

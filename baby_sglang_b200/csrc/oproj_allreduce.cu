@@ -57,7 +57,8 @@ constexpr int kOpSmemBytes = kOpStages * kOpStageBytes + 1024 /*alignment slack*
 struct OprojComm {
   uint8_t* staging[kOpMaxWorld];    // per rank: [world * max_slots] partial tiles (chunk-major 16-byte layout)
   uint8_t* out[kOpMaxWorld];        // per rank: [max_tokens * hidden] bf16
-  uint32_t* flags[kOpMaxWorld];     // per rank: arrive[max_slots][8], done[max_tiles], then {epoch, finished CTAs}
+  uint32_t* flags[kOpMaxWorld];     // per rank: arrive[max_slots][8], done[max_tiles], {epoch, finished CTAs}, then a
+                                    // 4 x u64 phase-timestamp record per CTA (globaltimer; read by comm.trace())
   uint8_t* mc_staging;              // multicast (NVLS) views of the same two regions; nullptr = peer-store path
   uint8_t* mc_out;
 };
@@ -223,6 +224,14 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
   const bool nvls = comm.mc_staging != nullptr;
   uint32_t* ctl = comm.flags[rank] + max_slots * kOpMaxWorld + max_tiles;   // {epoch of the last finished call, CTAs done}
   const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(ctl) + 1u;   // advanced by the last CTA of each launch
+  // phase timestamps of this CTA: {entry, last partial tile published, last owned tile delivered, exit}
+  uint64_t* trace = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(comm.flags[rank]) +
+                                                ((((size_t)max_slots * kOpMaxWorld + max_tiles + 2) * 4 + 1023) & ~(size_t)1023)) +
+                    4 * blockIdx.x;
+  if (threadIdx.x == 0) {
+    trace[0] = globaltimer_ns();
+    trace[1] = trace[2] = 0;
+  }
 
   const uint32_t bar0 = base + kOpStages * kOpStageBytes;
   const uint32_t full0 = bar0, empty0 = bar0 + 8 * kOpStages, accf0 = empty0 + 8 * kOpStages, acce0 = accf0 + 16;
@@ -328,6 +337,7 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
       named_bar_sync(1, 128);      // bar.sync orders the 128 threads' stores before thread 0's release (cumulative)
       if (etid == 0) st_release_sys(comm.flags[owner] + slot * kOpMaxWorld + rank, epoch);
     }
+    if (etid == 0) trace[1] = globaltimer_ns();
 
     // ---- phase 3: the local output is complete once every owner delivered every tile
     if (blockIdx.x == 0) {
@@ -362,6 +372,7 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
       named_bar_sync(2, 128);      // CTA-scope order of everyone's stores before the cumulative sys-scope release
       if (etid < world) st_release_sys(comm.flags[etid] + done_off + tile, epoch);
     }
+    if (etid == 0) trace[2] = globaltimer_ns();
 
   }
 
@@ -372,6 +383,7 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
   }
   // the last CTA to get here closes the call: every CTA has read `epoch` by now, none will read it again
   if (threadIdx.x == 0) {
+    trace[3] = globaltimer_ns();
     __threadfence();
     if (atomicAdd(ctl + 1, 1u) == gridDim.x - 1) {
       ctl[1] = 0u;

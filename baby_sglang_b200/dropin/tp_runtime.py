@@ -169,7 +169,9 @@ class FusedOProjAllReduce:
         staging_bytes = world_size * self.max_slots * self.TILE * self.TILE * 2
         self._off_out = up(staging_bytes)
         self._off_flags = self._off_out + self.out_bytes
-        self.nbytes = self._off_flags + up((self.max_slots * 8 + self.max_tiles + 2) * 4)
+        self._n_flag_words = self.max_slots * 8 + self.max_tiles + 2
+        self._off_trace = self._off_flags + up(self._n_flag_words * 4)              # 8-byte aligned
+        self.nbytes = self._off_trace + up(256 * 4 * 8)
         self._mine = None
         self._peers = []
         self._symm = None
@@ -252,6 +254,21 @@ class FusedOProjAllReduce:
         self._ops.oproj_allreduce(attn_out, weight, self.rank, self.world, *self._ptr_tables, self.max_slots,
                                   self.max_tiles, self.out_bytes, self._mc_staging, self._mc_out, self.timeout_s)
         return self._out_view[:T]
+
+    def trace(self):
+        """Phase timestamps of the LAST call, per CTA, in microseconds after the first CTA's entry:
+        rows {entry, last partial tile published, last owned tile delivered, exit} (0 where a CTA had no such work).
+        Diagnostics only (one device->host copy)."""
+        torch.cuda.synchronize()
+        raw = _RawView.make(self._staging[self.rank] + self._off_trace, (256 * 4 * 2,), torch.int32, self.device)
+        t = raw.cpu().view(torch.int64).view(256, 4)
+        t = t[t[:, 0] > 0]
+        if t.numel():
+            t = t[t[:, 0] >= int(t[:, 0].max()) - 1_000_000]      # CTAs of the last launch only
+        t0 = int(t[:, 0].min()) if t.numel() else 0
+        rel = (t - t0).clamp(min=0).double() / 1e3
+        rel[t == 0] = 0.0
+        return rel
 
     def close(self) -> None:
         if self.world > 1 and dist.is_initialized():
