@@ -31,8 +31,7 @@ SIGNATURES = {
     "bsgl_build_extend_metadata": (c_int, [_l, _p, _p, _p, _i, _l, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "bsgl_gather_kv_indices": (c_int, [_p, _l, _p, _p, _i, _p, _p]),
     "bsgl_partial_sizes": (c_int, [_i, _i, _i, _i, POINTER(c_int64), POINTER(c_int64)]),
-    "bsgl_paged_attention": (c_int, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, c_float, _i, _p, _p, _p, _i, _i,
-                                      _p]),
+    "bsgl_paged_attention": (c_int, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, c_float, _i, _p, _p, _p, _i, _p]),
     "bsgl_merge_partials": (c_int, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
     "bsgl_rope_kv_store": (c_int, [_p, _l, _p, _p, _p, _p, _p, _l, _p, _l, _i, _i, _i, _i, _p]),
     "bsgl_greedy_sample": (c_int, [_p, _l, _i, _i, _p, _i, _p, _p, _p, _p, _p]),

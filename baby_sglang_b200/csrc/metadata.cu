@@ -5,6 +5,8 @@
 // 117-125).  Also emits the split-KV plan consumed by the paged-attention kernel.
 //
 // Integer work on a few KB: one 1024-thread CTA, warp-shuffle block scans, no host sync.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace bsgl {
@@ -45,11 +47,10 @@ __device__ __forceinline__ unsigned long long pack(unsigned hi, unsigned lo) {
   return ((unsigned long long)hi << 32) | lo;
 }
 
-// Writes plan_hdr and cta_first_seq (2 * (n_ctas + 1) ints: the table, then zeroed merge counters) once
-// tile_indptr[0..n_seqs] is complete (caller synced).
-__device__ void finish_plan(int n_tiles, int n_seqs, int n_ctas, int32_t* plan_hdr, const int32_t* tile_indptr,
-                            int32_t* cta_first_seq) {
-  int n_eff = n_tiles / BSGL_MIN_TILES_PER_CTA;
+// Writes plan_hdr and cta_first_seq once tile_indptr[0..n_seqs] is complete (caller synced).
+__device__ void finish_plan(int n_tiles, int n_seqs, int n_ctas, int min_tiles, int32_t* plan_hdr,
+                            const int32_t* tile_indptr, int32_t* cta_first_seq) {
+  int n_eff = n_tiles / min_tiles;
   if (n_eff > n_ctas) n_eff = n_ctas;
   if (n_eff < 1) n_eff = 1;
   if (threadIdx.x == 0) {
@@ -71,9 +72,6 @@ __device__ void finish_plan(int n_tiles, int n_seqs, int n_ctas, int32_t* plan_h
       j = lo;
     }
     cta_first_seq[c] = j;
-    // second half of the buffer: the fused merge's per-sequence arrival counters (paged_attention.cu), zeroed
-    // here once per batch; their last user of every launch resets them
-    cta_first_seq[n_ctas + 1 + c] = 0;
   }
 }
 
@@ -81,7 +79,7 @@ __global__ void __launch_bounds__(kMetaThreads) decode_metadata_kernel(
     int64_t C, const int64_t* __restrict__ rpi, const int64_t* __restrict__ seq_lens, int B, int nhg, int n_ctas,
     int64_t* __restrict__ positions, int32_t* __restrict__ kv_indptr, int32_t* __restrict__ qo_indptr,
     int64_t* __restrict__ row_idx_off, int32_t* __restrict__ row_kv_len, int32_t* __restrict__ plan_hdr,
-    int32_t* __restrict__ tile_indptr, int32_t* __restrict__ cta_first_seq) {
+    int32_t* __restrict__ tile_indptr, int32_t* __restrict__ cta_first_seq, int min_tiles) {
   __shared__ unsigned long long warp_tot[33];
   unsigned carry_kv = 0, carry_tiles = 0;
   for (int base = 0; base < B; base += kMetaThreads) {
@@ -109,7 +107,7 @@ __global__ void __launch_bounds__(kMetaThreads) decode_metadata_kernel(
     tile_indptr[(int64_t)B * nhg] = n_tiles;
   }
   __syncthreads();
-  finish_plan(n_tiles, B * nhg, n_ctas, plan_hdr, tile_indptr, cta_first_seq);
+  finish_plan(n_tiles, B * nhg, n_ctas, min_tiles, plan_hdr, tile_indptr, cta_first_seq);
 }
 
 __global__ void __launch_bounds__(kMetaThreads) extend_metadata_kernel(
@@ -118,7 +116,7 @@ __global__ void __launch_bounds__(kMetaThreads) extend_metadata_kernel(
     int64_t* __restrict__ extended_lens, int64_t* __restrict__ positions, int32_t* __restrict__ qo_indptr,
     int32_t* __restrict__ kv_indptr, int64_t* __restrict__ row_idx_off, int32_t* __restrict__ row_kv_len,
     int32_t* __restrict__ plan_hdr, int32_t* __restrict__ tile_indptr, int32_t* __restrict__ cta_first_seq,
-    int32_t* __restrict__ heavy_order) {
+    int32_t* __restrict__ heavy_order, int min_tiles) {
   __shared__ unsigned long long warp_tot[33];
   // phase 0: requests by descending seq_len (rank by counting; ties keep index order)
   if (heavy_order != nullptr) {
@@ -194,7 +192,7 @@ __global__ void __launch_bounds__(kMetaThreads) extend_metadata_kernel(
     const int n_tiles = (int)(carry_tiles * nhg);
     if (threadIdx.x == 0) tile_indptr[T * nhg] = n_tiles;
     __syncthreads();
-    finish_plan(n_tiles, (int)(T * nhg), n_ctas, plan_hdr, tile_indptr, cta_first_seq);
+    finish_plan(n_tiles, (int)(T * nhg), n_ctas, min_tiles, plan_hdr, tile_indptr, cta_first_seq);
   }
 }
 
@@ -207,6 +205,18 @@ __global__ void __launch_bounds__(256) gather_kv_indices_kernel(const int32_t* _
   const int32_t* row = req_to_token + rpi[i] * C;
   for (int p = blockIdx.y * blockDim.x + threadIdx.x; p < end - begin; p += gridDim.y * blockDim.x)
     kv_indices[begin + p] = row[p];
+}
+
+// A CTA of the split-KV kernel gets at least this many 16-token tiles, so short batches use fewer CTAs and their
+// sequences are cut into fewer partials.  BSGL_MIN_TILES_PER_CTA (4) is the measured default; the environment
+// variable of the same name overrides it for tuning runs (read once).
+static int min_tiles_per_cta() {
+  static const int v = [] {
+    const char* e = getenv("BSGL_MIN_TILES_PER_CTA");
+    const int x = e ? atoi(e) : BSGL_MIN_TILES_PER_CTA;
+    return x >= 1 ? x : BSGL_MIN_TILES_PER_CTA;
+  }();
+  return v;
 }
 
 }  // namespace bsgl
@@ -225,7 +235,7 @@ int bsgl_build_decode_metadata(int64_t page_table_stride, const int64_t* req_poo
   BSGL_REQUIRE(batch == 0 || (req_pool_indices && seq_lens), "bsgl_build_decode_metadata: null input");
   decode_metadata_kernel<<<1, kMetaThreads, 0, (cudaStream_t)stream>>>(
       page_table_stride, req_pool_indices, seq_lens, batch, n_head_groups, n_ctas, positions, kv_indptr, qo_indptr,
-      row_idx_off, row_kv_len, plan_hdr, tile_indptr, cta_first_seq);
+      row_idx_off, row_kv_len, plan_hdr, tile_indptr, cta_first_seq, min_tiles_per_cta());
   return check_launch("decode_metadata_kernel");
 }
 
@@ -246,7 +256,7 @@ int bsgl_build_extend_metadata(int64_t page_table_stride, const int64_t* req_poo
   extend_metadata_kernel<<<1, kMetaThreads, 0, (cudaStream_t)stream>>>(
       page_table_stride, req_pool_indices, seq_lens, prefix_lens, batch, n_tokens, n_head_groups, n_ctas,
       extended_lens, positions, qo_indptr, kv_indptr, row_idx_off, row_kv_len, plan_hdr, tile_indptr, cta_first_seq,
-      heavy_order);
+      heavy_order, min_tiles_per_cta());
   return check_launch("extend_metadata_kernel");
 }
 

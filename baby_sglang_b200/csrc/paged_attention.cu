@@ -23,11 +23,6 @@
 //     from ldmatrix.trans).  fp32 accumulation throughout.
 //   * per item: the NSUB partial states of each head are merged through shared memory and either
 //     the final row (bf16/fp16) or a normalised fp32 partial + base-2 LSE is written.
-//   * split sequences (K2c fused in, `fuse_merge`): a sequence is split only where a CTA boundary falls inside
-//     it.  Every CTA that wrote one of its partials bumps the sequence's counter (kept next to the plan, indexed
-//     by the first CTA of the sequence, zeroed by K4 and reset by its last user); the CTA that arrives LAST
-//     reads the partials back (a few KB) and writes the merged row -- no second launch, no dependent-grid
-//     hand-over on the critical path of small batches.
 //
 // HBM-bound: algorithmic bytes per launch = sum(kv_len) * Hkv * D * 2 * e (+ page table + q/out).
 #include "common.cuh"
@@ -50,8 +45,6 @@ struct Item {
   int tok_end;         // one past the last KV token
   int part_slot;       // -1: write the final row; else partial slot
   int valid;
-  int seq;             // sequence index (row * n_head_groups + hg)
-  int pad;
 };
 
 template <int D, int HPB>
@@ -81,7 +74,7 @@ struct Cfg {
   static constexpr int SCR_BYTES = kConsumerWarps * SCR_FLOATS * 4;
   static constexpr int ML_BYTES = kConsumerWarps * 8 * 2 * 4;
   static constexpr int ITEM_BYTES = kMaxItems * (int)sizeof(Item);
-  static constexpr int FIXED_BYTES = SCR_BYTES + ML_BYTES + ITEM_BYTES + 1024 /*barriers + merge flag + slack*/;
+  static constexpr int FIXED_BYTES = SCR_BYTES + ML_BYTES + ITEM_BYTES + 1024 /*barriers + slack*/;
   static constexpr int NSTAGES_RAW = (kSmemBudget - FIXED_BYTES) / STAGE_BYTES;
   static constexpr int NSTAGES_CAP = NSTAGES_RAW > 24 ? 24 : NSTAGES_RAW;
   // WPT: a stage must belong to the same producer warp in every round (NSTAGES % 4 == 0).  Otherwise the warp
@@ -99,7 +92,7 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
                        const int32_t* __restrict__ row_kv_len, const int32_t* __restrict__ plan_hdr,
                        const int32_t* __restrict__ tile_indptr, const int32_t* __restrict__ cta_first_seq,
                        int n_q_heads, int n_kv_heads, float scale_log2, T* __restrict__ out,
-                       float* __restrict__ part_o, float* __restrict__ part_lse, int fuse_merge) {
+                       float* __restrict__ part_o, float* __restrict__ part_lse) {
   using C = Cfg<D, HPB>;
   constexpr int NST = C::NSTAGES;
   constexpr int NSUB = C::NSUB;
@@ -113,9 +106,6 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(items) + C::ITEM_BYTES);
   const uint32_t full_bar0 = smem_u32(bars);
   const uint32_t empty_bar0 = smem_u32(bars + NST);
-  volatile int* merge_flag = reinterpret_cast<volatile int*>(bars + 2 * NST);   // consumers only
-  // per-sequence arrival counters of the fused merge: second half of the cta_first_seq buffer (zeroed by K4)
-  int32_t* merge_ctr = const_cast<int32_t*>(cta_first_seq) + gridDim.x + 1;
   const uint32_t stages_u32 = smem_u32(stages);
 
   const int warp = threadIdx.x >> 5;
@@ -147,19 +137,6 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
   // (cta_first_seq has gridDim.x + 1 entries whatever n_eff is)
   const int seq_first = cta_first_seq[cta];
   int seq_last = cta_first_seq[cta + 1];
-  if (fuse_merge && (n_tiles == 0 || cta == 0)) {
-    // rows with no KV tokens are defined as zeros.  Sequences without tiles that sit between two sequences with
-    // tiles are zero-filled by the CTA that walks past them (below); those BEFORE the first tile (all of them when
-    // there is no tile at all) belong to no CTA's range and are done here.
-    const int lead = n_tiles == 0 ? n_seqs : seq_first;
-    const int heads = HPB * G;
-    for (int j = threadIdx.x; j < lead; j += blockDim.x) {
-      if (n_tiles == 0 && (j % (int)gridDim.x) != cta) continue;      // no tiles at all: every CTA takes a share
-      const int row = j / nhg, hg = j - row * nhg;
-      T* orow = out + ((int64_t)row * n_q_heads + (int64_t)hg * heads) * D;
-      for (int e = 0; e < heads * D; e += 8) *reinterpret_cast<uint4*>(orow + e) = make_uint4(0u, 0u, 0u, 0u);
-    }
-  }
   if (cta >= n_eff || n_tiles == 0) return;
 
   const int tile_lo = cta_tile_begin(cta, n_tiles, n_eff);
@@ -177,15 +154,8 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
       const int lo = max(tb, tile_lo), hi = min(te, tile_hi);
       Item it;
       it.valid = lo < hi;
-      it.seq = j;
-      it.pad = 0;
       it.row = j / nhg;
       it.hg = j - it.row * nhg;
-      if (fuse_merge && tb == te && j > seq_first) {
-        // an empty sequence inside this CTA's range (never the range's first: that one holds a tile)
-        T* orow = out + ((int64_t)it.row * n_q_heads + (int64_t)it.hg * (HPB * G)) * D;
-        for (int e = 0; e < HPB * G * D; e += 8) *reinterpret_cast<uint4*>(orow + e) = make_uint4(0u, 0u, 0u, 0u);
-      }
       const int kvl = row_kv_len[it.row];
       it.idx_off = row_idx_off[it.row];
       it.tok_begin = (lo - tb) * kTile;
@@ -505,51 +475,7 @@ paged_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, co
           if (it.part_slot >= 0 && lane == 0)
             part_lse[(int64_t)it.part_slot * (HPB * G) + pair] = mm + log2f(den);
         }
-        if (fuse_merge && it.part_slot >= 0) __threadfence();   // this CTA's partial is visible device-wide ...
         named_bar_sync(1, kConsumerWarps * 32);   // scratch may be overwritten by the next item
-
-        if (fuse_merge && it.part_slot >= 0) {
-          // ---- fused LSE merge: the last of the sequence's CTAs to get here combines every partial
-          const int tb = tile_indptr[it.seq], te = tile_indptr[it.seq + 1];
-          const int c_first = cta_of_tile(tb, n_tiles, n_eff), c_last = cta_of_tile(te - 1, n_tiles, n_eff);
-          if (warp == 0 && lane == 0) {
-            const int prev = atomicAdd(merge_ctr + c_first, 1);        // ... before it is counted
-            const int last = prev == c_last - c_first;
-            if (last) merge_ctr[c_first] = 0;                          // ready for the plan's next launch
-            *merge_flag = last;
-          }
-          named_bar_sync(1, kConsumerWarps * 32);
-          if (*merge_flag) {
-            __threadfence();                                           // the other CTAs' partials, after the count
-            const int heads = HPB * G;
-            for (int pair = warp; pair < heads; pair += kConsumerWarps) {
-              const int dd = lane * 4;
-              float m = -INFINITY, den = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll 4
-              for (int c = c_first; c <= c_last; ++c) {
-                const int64_t slot = 2 * c + (c == c_first ? 1 : 0);
-                const float lse = __ldcg(part_lse + slot * heads + pair);
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (dd < D) v = __ldcg(reinterpret_cast<const float4*>(part_o + (slot * heads + pair) * D + dd));
-                const float mn = fmaxf(m, lse);
-                const float sc = fast_exp2(m - mn), w = fast_exp2(lse - mn);   // m = -inf on the first part: sc = 0
-                den = den * sc + w;
-                a0 = a0 * sc + w * v.x; a1 = a1 * sc + w * v.y; a2 = a2 * sc + w * v.z; a3 = a3 * sc + w * v.w;
-                m = mn;
-              }
-              if (dd < D) {
-                const float inv = 1.f / den;
-                const int ph_ = pair / G, pg = pair - ph_ * G;
-                const int qh = (it.hg * HPB + ph_) * G + pg;
-                uint2 pk;
-                pk.x = pack2<T>(a0 * inv, a1 * inv);
-                pk.y = pack2<T>(a2 * inv, a3 * inv);
-                *reinterpret_cast<uint2*>(out + ((int64_t)it.row * n_q_heads + qh) * D + dd) = pk;
-              }
-            }
-          }
-          named_bar_sync(1, kConsumerWarps * 32);                      // merge_flag may be rewritten by the next item
-        }
       }
     }
   }
@@ -561,7 +487,7 @@ static int launch_paged_attention(const void* q, const void* k_slab, const void*
                                   const int64_t* row_idx_off, const int32_t* row_kv_len, const int32_t* plan_hdr,
                                   const int32_t* tile_indptr, const int32_t* cta_first_seq, int n_q_heads,
                                   int n_kv_heads, float sm_scale, void* out, float* part_o, float* part_lse,
-                                  int n_ctas, int fuse_merge, cudaStream_t stream) {
+                                  int n_ctas, cudaStream_t stream) {
   using C = Cfg<D, HPB>;
   auto kern = paged_attention_kernel<T, D, HPB>;
   static thread_local int configured_dev = -1;
@@ -584,7 +510,7 @@ static int launch_paged_attention(const void* q, const void* k_slab, const void*
   cfg.numAttrs = 1;
   BSGL_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, (const T*)q, (const T*)k_slab, (const T*)v_slab, idx_base, row_idx_off,
                                    row_kv_len, plan_hdr, tile_indptr, cta_first_seq, n_q_heads, n_kv_heads,
-                                   scale_log2, (T*)out, part_o, part_lse, fuse_merge));
+                                   scale_log2, (T*)out, part_o, part_lse));
   return check_launch("paged_attention_kernel");
 }
 
@@ -594,7 +520,7 @@ extern "C" int bsgl_paged_attention(const void* q, const void* k_slab, const voi
                                     const int64_t* row_idx_off, const int32_t* row_kv_len, const int32_t* plan_hdr,
                                     const int32_t* tile_indptr, const int32_t* cta_first_seq, int n_rows,
                                     int n_q_heads, int n_kv_heads, int head_dim, float sm_scale, int dtype, void* out,
-                                    float* part_o, float* part_lse, int n_ctas, int fuse_merge, void* stream) {
+                                    float* part_o, float* part_lse, int n_ctas, void* stream) {
   using namespace bsgl;
   BSGL_REQUIRE(n_rows >= 0, "bsgl_paged_attention: negative row count");
   if (n_rows == 0) return BSGL_OK;
@@ -615,7 +541,7 @@ extern "C" int bsgl_paged_attention(const void* q, const void* k_slab, const voi
 #define BSGL_PA(T, D, H)                                                                                          \
   return launch_paged_attention<T, D, H>(q, k_slab, v_slab, idx_base, row_idx_off, row_kv_len, plan_hdr,          \
                                          tile_indptr, cta_first_seq, n_q_heads, n_kv_heads, sm_scale, out, part_o, \
-                                         part_lse, n_ctas, fuse_merge, s)
+                                         part_lse, n_ctas, s)
 #define BSGL_PA_D(T, H)                \
   do {                                 \
     if (head_dim == 128) BSGL_PA(T, 128, H); \

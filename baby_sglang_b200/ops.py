@@ -168,7 +168,7 @@ class AttnPlan:
     row_kv_len: torch.Tensor       # int32 [rows]
     plan_hdr: torch.Tensor         # int32 [4]  {n_tiles, n_ctas_eff, n_seqs, 0}
     tile_indptr: torch.Tensor      # int32 [rows*nhg + 1]
-    cta_first_seq: torch.Tensor    # int32 [2 * (n_ctas + 1)]: table, then zeroed merge counters
+    cta_first_seq: torch.Tensor    # int32 [n_ctas + 1]
 
 
 @dataclass
@@ -207,7 +207,7 @@ def _plan_buffers(dev, n_rows: int, nhg: int, n_ctas: int):
     i32 = dict(dtype=torch.int32, device=dev)
     return (torch.empty(n_rows, dtype=torch.int64, device=dev), torch.empty(n_rows, **i32),
             torch.empty(_lib.PLAN_HDR_INTS, **i32), torch.empty(n_rows * nhg + 1, **i32),
-            torch.empty(2 * (n_ctas + 1), **i32))     # the table, then the fused merge's arrival counters
+            torch.empty(n_ctas + 1, **i32))
 
 
 def _as_i64(t: torch.Tensor) -> torch.Tensor:
@@ -301,14 +301,11 @@ def partial_buffers(dev, n_ctas: int, n_q_heads: int, n_kv_heads: int, head_dim:
 def paged_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor, idx_base: torch.Tensor,
                     plan: AttnPlan, sm_scale: float, out: Optional[torch.Tensor] = None,
                     workspace: Optional[Tuple[torch.Tensor, torch.Tensor]] = None,
-                    merge="fused") -> torch.Tensor:
+                    merge: bool = True) -> torch.Tensor:
     """One q row per plan row over the paged KV; returns [rows, Hq*D] in q's dtype.
 
-    Replaces `_decode_attention` (attn_backend.py:112-149): ONE launch of K2, which also merges the sequences it
-    split across CTAs (`merge="fused"`, the default; `True` means the same).  `merge="separate"` runs the merge as
-    its own kernel (K2c) instead, `merge=False` leaves the partials unmerged (kernel timing).
-    `idx_base` is the int32 page table (`req_to_token`) or a flattened `kv_indices`.  A plan must not be used by
-    two launches at once (its arrival counters are shared); launches on one stream are fine.
+    Replaces `_decode_attention` (attn_backend.py:112-149): K2 split-KV partial pass + K2c merge.
+    `idx_base` is the int32 page table (`req_to_token`) or a flattened `kv_indices`.
     """
     dev = _require_cuda(q, k_slab, v_slab, idx_base)
     if q.dim() != 3:
@@ -337,10 +334,10 @@ def paged_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor,
         q.data_ptr(), k_slab.data_ptr(), v_slab.data_ptr(), idx_base.data_ptr(), plan.row_idx_off.data_ptr(),
         plan.row_kv_len.data_ptr(), plan.plan_hdr.data_ptr(), plan.tile_indptr.data_ptr(),
         plan.cta_first_seq.data_ptr(), rows, Hq, Hkv, D, float(sm_scale), code, out.data_ptr(),
-        part_o.data_ptr(), part_lse.data_ptr(), plan.n_ctas, 1 if merge in (True, "fused") else 0, st)
+        part_o.data_ptr(), part_lse.data_ptr(), plan.n_ctas, st)
     _lib.check(rc, "bsgl_paged_attention")
     _count()
-    if merge == "separate":
+    if merge:
         rc = lib.bsgl_merge_partials(part_o.data_ptr(), part_lse.data_ptr(), plan.plan_hdr.data_ptr(),
                                      plan.tile_indptr.data_ptr(), plan.cta_first_seq.data_ptr(), plan.n_ctas,
                                      rows, Hq, Hkv, D, code, out.data_ptr(), st)

@@ -89,8 +89,7 @@ int bsgl_kv_store(void* k_slab, void* v_slab, int64_t n_slots, const int32_t* lo
  *   qo_indptr   int32 [B+1]    0..B
  *   row_idx_off int64 [B]      element offset of the row's token list inside req_to_token
  *   row_kv_len  int32 [B]      KV tokens the row attends to (= seq_lens)
- *   plan_hdr    int32 [4], tile_indptr int32 [B*n_head_groups+1], cta_first_seq int32 [2*(n_ctas+1)] (the table,
- *               then n_ctas+1 zeroed arrival counters for the fused split-KV merge)
+ *   plan_hdr    int32 [4], tile_indptr int32 [B*n_head_groups+1], cta_first_seq int32 [n_ctas+1]
  *                              the split-KV plan for bsgl_paged_attention */
 int bsgl_build_decode_metadata(int64_t page_table_stride, const int64_t* req_pool_indices,
                                const int64_t* seq_lens, int batch, int n_head_groups, int n_ctas,
@@ -106,7 +105,7 @@ int bsgl_build_decode_metadata(int64_t page_table_stride, const int64_t* req_poo
  *   qo_indptr     int32 [B+1], kv_indptr int32 [B+1]
  *   row_idx_off   int64 [T], row_kv_len int32 [T]  per q token: its request's page-table row
  *                              and prefix + local_row + 1 (mask col <= prefix+row, attn_backend.py:83-85)
- *   plan_hdr / tile_indptr [T*n_head_groups+1] / cta_first_seq [2*(n_ctas+1)]: row-wise plan
+ *   plan_hdr / tile_indptr [T*n_head_groups+1] / cta_first_seq [n_ctas+1]: row-wise plan
  *                              (may be NULL when the row-wise kernel will not be used).
  *   heavy_order   int32 [B]    request indices by descending seq_len (ties by index): the dispatch
  *                              order of bsgl_extend_attention's CTAs (may be NULL). */
@@ -134,16 +133,14 @@ int bsgl_partial_sizes(int n_ctas, int n_q_heads, int n_kv_heads, int head_dim,
  * owns an equal contiguous range of 16-token tiles of the flattened (row, head-group) space, so
  * long and ragged contexts split across CTAs.  Sequences that fall entirely inside one CTA are
  * written to `out` directly; the others leave normalised partials + base-2 LSE in
- * part_o/part_lse.  fuse_merge != 0: the last CTA to finish a split sequence merges its partials itself (per-sequence
- * arrival counters in the second half of the cta_first_seq buffer, which is 2 * (n_ctas + 1) ints; rows without KV
- * tokens are zero-filled), so the call is complete by itself; fuse_merge == 0: bsgl_merge_partials does both. */
+ * part_o/part_lse for bsgl_merge_partials. */
 int bsgl_paged_attention(const void* q, const void* k_slab, const void* v_slab,
                          const int32_t* idx_base, const int64_t* row_idx_off,
                          const int32_t* row_kv_len, const int32_t* plan_hdr,
                          const int32_t* tile_indptr, const int32_t* cta_first_seq,
                          int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
                          float sm_scale, int dtype, void* out,
-                         float* part_o, float* part_lse, int n_ctas, int fuse_merge, void* stream);
+                         float* part_o, float* part_lse, int n_ctas, void* stream);
 
 /* K2c.  LSE merge of the partials of every sequence that was split; rows with no KV tokens
  * get zeros.  Must follow bsgl_paged_attention on the same stream with the same plan and n_ctas

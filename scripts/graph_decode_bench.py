@@ -1,4 +1,4 @@
-"""Small-batch decode step (K4 + L x (K1, K2 [, K2c])): eager launches vs one CUDA-graph replay.
+"""Small-batch decode step (K4 + L x (K1, K2, K2c)): eager launches vs one CUDA-graph replay.
 
 At small batch the kernels are short (tens of microseconds) and the Python/driver launch path dominates an eager
 step; the step makes no host sync, so it captures into one graph (programmatic dependent launches included) and a
@@ -23,8 +23,6 @@ def main():
     ap.add_argument("--ctx", type=int, default=4096)
     ap.add_argument("--layers", type=int, default=28)
     ap.add_argument("--iters", type=int, default=30)
-    ap.add_argument("--merge", default="fused", choices=["fused", "separate"],
-                    help="split-KV merge inside K2 (default) or as the separate K2c launch")
     a = ap.parse_args()
     Hq, Hkv, D = 28, 4, 128                                   # Qwen2.5-7B
     dev = torch.device("cuda")
@@ -50,7 +48,7 @@ def main():
         md = ops.build_decode_metadata(r2t, rpi, seq, Hkv)
         for l in range(L):
             ops.kv_store(slabs[l][0], slabs[l][1], loc, k, v)
-            ops.paged_attention(q, slabs[l][0], slabs[l][1], r2t, md.plan, scale, out=outs[l], merge=a.merge)
+            ops.paged_attention(q, slabs[l][0], slabs[l][1], r2t, md.plan, scale, out=outs[l])
 
     def timed(fn):
         for _ in range(5):
@@ -78,7 +76,7 @@ def main():
     graph_ms = timed(graph.replay)
     same = all(torch.equal(x, y) for x, y in zip(ref, outs))
     bytes_ = L * (B * a.ctx * Hkv * D * 2 * 2 + 4 * B * a.ctx + 2 * B * Hq * D * 2)
-    print(json.dumps({"batch": B, "ctx": a.ctx, "layers": L, "merge": a.merge, "eager_ms_per_step": round(eager_ms, 4),
+    print(json.dumps({"batch": B, "ctx": a.ctx, "layers": L, "eager_ms_per_step": round(eager_ms, 4),
                       "graph_ms_per_step": round(graph_ms, 4), "speedup": round(eager_ms / graph_ms, 2),
                       "graph_us_per_layer": round(graph_ms / L * 1e3, 1),
                       "graph_GBps": round(bytes_ / graph_ms / 1e6, 1), "replay_bit_identical": same}))
