@@ -15,6 +15,7 @@ from . import LIB_PATH
 BF16, F16, F32 = 0, 1, 2
 TILE_TOKENS = 16
 PLAN_HDR_INTS = 4
+MIN_TILES_PER_CTA = 16     # BSGL_MIN_TILES_PER_CTA in the header
 
 _i = c_int
 _l = c_int64

@@ -142,7 +142,12 @@ class FusedOProjAllReduce:
     peer mapping and the NVSwitch MULTICAST mapping; `exchange = "nvls"`): partial tiles then stay in each rank's
     own staging and the tile's owner reduces them inside the switch (`multimem.ld_reduce`) and broadcasts the sum
     (`multimem.st`).  Without multicast support the buffers are cudaMalloc + CUDA IPC through the C ABI and
-    partial tiles travel by peer stores (`exchange = "peer-stores"`).  `BSGL_K8_EXCHANGE=peer` forces the latter.
+    partial tiles travel by peer stores (`exchange = "peer-stores"`).  The choice is made PER CALL: the in-switch
+    reduction halves the bytes on the wire but its request chain (flag -> multimem.ld_reduce -> multimem.st -> flag)
+    is a few microseconds longer than the peer-store chain, so it is used where the exchange is bandwidth-bound
+    (world >= 4 and at least BSGL_K8_NVLS_MIN_BYTES, default 4 MiB, of reduced output); measured on B200s, see
+    DESIGN.md.  `BSGL_K8_EXCHANGE` = `peer` (IPC buffers, peer stores only), `symm-peer` (symmetric memory, peer
+    stores only) or `nvls` (always) overrides it.
 
     Every rank must make the same sequence of calls, which the replicated scheduler guarantees; the call counter
     lives in device memory, so the call can sit inside a captured CUDA graph.  The returned tensor is a view of
@@ -177,12 +182,19 @@ class FusedOProjAllReduce:
         self._symm = None
         mc = 0
         base = None
-        if world_size > 1 and os.environ.get("BSGL_K8_EXCHANGE", "") != "peer":
+        mode = os.environ.get("BSGL_K8_EXCHANGE", "")
+        if world_size > 1 and mode != "peer":
             base, mc = self._alloc_symmetric()
         if base is None:
             base = self._alloc_ipc()
-        self.exchange = "nvls (multimem.ld_reduce / multimem.st over the NVSwitch multicast mapping)" if mc else \
+        if mode == "symm-peer":
+            mc = 0
+        self._nvls_always = mode == "nvls"
+        self._nvls_min_bytes = int(os.environ.get("BSGL_K8_NVLS_MIN_BYTES", str(4 << 20)))
+        self.exchange = ("nvls for large reductions (multimem.ld_reduce / multimem.st over the NVSwitch multicast "
+                         "mapping), peer stores for small ones") if mc else \
             ("peer-stores (two-shot over NVLink peer memory)" if world_size > 1 else "local (world 1)")
+        self.last_exchange = None
         self._staging = base
         self._out = [p + self._off_out for p in base]
         self._flags = [p + self._off_flags for p in base]
@@ -251,8 +263,13 @@ class FusedOProjAllReduce:
         if attn_out.dtype != self.dtype or weight.dtype != self.dtype or int(weight.shape[0]) != self.hidden:
             raise ValueError("dtype / hidden size differ from the communicator's")
         self.calls += 1
+        # same decision on every rank: it depends on the call's shape only
+        nvls = bool(self._mc_staging) and (self._nvls_always or
+                                           (self.world >= 4 and T * self.hidden * 2 >= self._nvls_min_bytes))
+        self.last_exchange = "nvls" if nvls else ("peer-stores" if self.world > 1 else "local")
         self._ops.oproj_allreduce(attn_out, weight, self.rank, self.world, *self._ptr_tables, self.max_slots,
-                                  self.max_tiles, self.out_bytes, self._mc_staging, self._mc_out, self.timeout_s)
+                                  self.max_tiles, self.out_bytes, self._mc_staging if nvls else 0,
+                                  self._mc_out if nvls else 0, self.timeout_s)
         return self._out_view[:T]
 
     def trace(self):

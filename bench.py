@@ -469,7 +469,7 @@ def measure_decode_workload(workload, rank, world, device, steps, warmup, oproj=
             k8_ms, _ = timed(lambda: fused_comm(x, w_o), 20, 5)
             res["allreduce"]["k8_fused_us"] = round(k8_ms * 1e3, 2)
             res["allreduce"]["k8_busbw_GBps"] = round(2 * (world - 1) / world * nbytes / k8_ms / 1e6, 1)
-            res["allreduce"]["k8_exchange"] = fused_comm.exchange
+            res["allreduce"]["k8_exchange"] = fused_comm.last_exchange
     if fused_comm is not None:
         fused_comm.close()      # collective (barrier): every rank, before the others leave
     del w, qkv_dev, qkv_split_dev, fb, attn0
@@ -614,6 +614,69 @@ def measure_small_kernels(device):
     return out
 
 
+def measure_small_batch(device, ctx=4096, iters=30):
+    """Small decode batches are launch-bound when launched eagerly (~37 us of host time per layer); the step makes
+    no host sync and takes every size from device buffers, so it replays as ONE CUDA graph.  Attention path of the
+    metric's geometry (28 layers: K4 + per layer K1, K2, K2c), B = 1, 4, 16."""
+    from baby_sglang_b200 import ops
+    Hq, Hkv, D, L = GEOMETRY["qwen2.5-7b"][:4]
+    out = {"workload": f"qwen2.5-7b attention path, ctx {ctx}, {L} layers per step, bf16", "cases": []}
+    g = torch.Generator(device=device).manual_seed(0)
+    for B in (1, 4, 16):
+        seq = torch.full((B,), ctx, device=device, dtype=torch.int64)
+        S = B * ctx + 64
+        perm = torch.randperm(S, generator=g, device=device).to(torch.int32) + 1
+        r2t = torch.zeros(B, ctx + 8, dtype=torch.int32, device=device)
+        r2t[:, :ctx] = perm[:B * ctx].view(B, ctx)
+        rpi = torch.arange(B, device=device)
+        loc = r2t[rpi, seq - 1].contiguous()
+        slabs = [(torch.randn(S + 1, Hkv, D, device=device, dtype=torch.bfloat16),
+                  torch.randn(S + 1, Hkv, D, device=device, dtype=torch.bfloat16)) for _ in range(L)]
+        q = torch.randn(B, Hq, D, device=device, dtype=torch.bfloat16)
+        k = torch.randn(B, Hkv, D, device=device, dtype=torch.bfloat16)
+        v = torch.randn(B, Hkv, D, device=device, dtype=torch.bfloat16)
+        outs = [torch.empty(B, Hq * D, device=device, dtype=torch.bfloat16) for _ in range(L)]
+
+        def step():
+            md = ops.build_decode_metadata(r2t, rpi, seq, Hkv)
+            for l in range(L):
+                ops.kv_store(slabs[l][0], slabs[l][1], loc, k, v)
+                ops.paged_attention(q, slabs[l][0], slabs[l][1], r2t, md.plan, D ** -0.5, out=outs[l])
+
+        def timed(fn):
+            for _ in range(5):
+                fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / iters
+
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            step()
+        side.synchronize()
+        eager = timed(step)
+        ref = [o.clone() for o in outs]
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            step()
+        for o in outs:
+            o.zero_()
+        replay = timed(graph.replay)
+        same = all(torch.equal(a, b) for a, b in zip(ref, outs))
+        nb = L * (decode_bytes(B * ctx, B, Hq, Hkv, D) + kv_store_bytes(B, Hkv, D))
+        out["cases"].append({"batch": B, "eager_ms_per_step": round(eager, 4), "graph_ms_per_step": round(replay, 4),
+                             "graph_us_per_layer": round(replay / L * 1e3, 1), "graph_GBps": round(nb / replay / 1e6, 1),
+                             "replay_bit_identical_to_eager": same})
+        del graph, slabs, outs
+        _free()
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 # the GPU arm
 # ------------------------------------------------------------------------------------------------
@@ -655,6 +718,7 @@ def run_b200(args, rank, world, device):
                 _free()
         if not args.skip_small:
             small = measure_small_kernels(device)
+            small["small_batch_decode"] = measure_small_batch(device)
     if rank != 0:
         return
     cpu = cpu_baseline(args.workload, seconds=15.0)

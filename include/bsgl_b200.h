@@ -49,7 +49,7 @@ extern "C" {
 
 #define BSGL_VERSION 100       /* 0.1.0 */
 #define BSGL_TILE_TOKENS 16    /* KV tokens per pipeline tile of the paged-attention kernel */
-#define BSGL_MIN_TILES_PER_CTA 4
+#define BSGL_MIN_TILES_PER_CTA 16  /* measured: B=1..4 decode 0.82 -> 0.59 ms per 28 layers vs 4 (fewer partials) */
 #define BSGL_PLAN_HDR_INTS 4   /* plan_hdr = { n_tiles, n_ctas_eff, n_seqs, reserved } */
 
 enum bsgl_dtype { BSGL_BF16 = 0, BSGL_F16 = 1, BSGL_F32 = 2 };

@@ -53,8 +53,8 @@ def main():
 
         line["nccl_pair_us"] = timed(pair, group, dev)
         line["gemm_only_us"] = timed(lambda: torch.nn.functional.linear(a, w), group, dev)
-        for mode in ("nvls", "peer"):
-            os.environ["BSGL_K8_EXCHANGE"] = "peer" if mode == "peer" else ""
+        for mode in ("nvls", "symm-peer", "peer"):
+            os.environ["BSGL_K8_EXCHANGE"] = mode
             comm = tp_runtime.FusedOProjAllReduce(rank, world, group, hidden=hidden, max_tokens=1024)
             us = timed(lambda: comm(a, w), group, dev)
             dist.barrier(group=group)
@@ -63,7 +63,7 @@ def main():
             def stat(col):
                 v = tr[:, col][tr[:, col] > 0]
                 return None if v.numel() == 0 else [round(float(v.median()), 1), round(float(v.max()), 1)]
-            line[mode] = {"exchange": comm.exchange.split(" ")[0], "us": us, "ctas": int(tr.shape[0]),
+            line[mode] = {"exchange": comm.last_exchange, "us": us, "ctas": int(tr.shape[0]),
                           "entry_spread_us": round(float(tr[:, 0].max()), 1),
                           "published_med_max_us": stat(1), "delivered_med_max_us": stat(2), "exit_med_max_us": stat(3)}
             comm.close()

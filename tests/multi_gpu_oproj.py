@@ -76,7 +76,7 @@ def main():
         good = same and replay_same and err_exact <= tol and err_nccl <= 2 * tol
         ok &= good
         line = {"case": f"T={T} hidden={hidden} K/rank={K}", "world": world, "bit_identical_across_ranks": same,
-                "cuda_graph_replays_identical": replay_same, "exchange": comm.exchange,
+                "cuda_graph_replays_identical": replay_same, "exchange": comm.last_exchange,
                 "max_abs_err_vs_fp32": err_exact, "max_abs_err_vs_nccl_pair": err_nccl, "tol": tol, "ok": good}
         if bench and T == 1024:
             def timed(fn, n=50):

@@ -70,7 +70,7 @@ def main():
                               tp=dict(rank=rank, world=world, group=group, fused=fused, mlp=mlp, max_tokens=2048))
         assert run.scheduler.token_to_kv_pool.head_num == CFG["num_key_value_heads"] // world
         runs = _run(run, prompts, forced=[r["ids"] for r in ref_runs])
-        line = {"variant": name, "world": world, "exchange": getattr(run.comm, "exchange", "nccl all_reduce")}
+        line = {"variant": name, "world": world, "exchange": getattr(run.comm, "last_exchange", "nccl all_reduce")}
         good = True
         for phase, (r, d) in zip(("cold", "radix-hit"), zip(ref_runs, runs)):
             same_state = all(torch.equal(r["state"][k], d["state"][k]) for k in ("req_to_token", "free_slots")) and \

@@ -9,6 +9,7 @@ import sys
 import pytest
 import torch
 
+from baby_sglang_b200 import _lib
 from oracle import paged_attention_oracle as O
 from tests.helpers import golden_names, load_golden, make_paged_case, slab_checksum
 
@@ -320,7 +321,7 @@ def test_decode_metadata_bit_exact(ops, nhg_heads, n_ctas):
     n_eff = hdr[1]
     tile_indptr, begins, first = O.split_plan(seq.tolist(), nhg, 16, n_eff)
     assert hdr[0] == tile_indptr[-1] and hdr[2] == B * nhg
-    assert n_eff == max(1, min(n_ctas, tile_indptr[-1] // 4))
+    assert n_eff == max(1, min(n_ctas, tile_indptr[-1] // _lib.MIN_TILES_PER_CTA))
     assert md.plan.tile_indptr.cpu().tolist() == tile_indptr
     assert md.plan.cta_first_seq.cpu().tolist()[: n_eff + 1] == first
 

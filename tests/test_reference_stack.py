@@ -15,7 +15,9 @@ so retraction never fires:
     margin is within 2 bf16 ulps (rounding noise decides the argmax in either stack).  Every such
     tie is written, with its margin, to gpurun_out/reference_stack_flips.json (committed copy:
     profiles/r2_reference_stack_flips.json); anything else fails the test.
-  * the same again with K5 + K6 + K7 installed on the instances (`model_hooks.install_*`).
+  * the same again with K5 + K6 + K7 installed on the instances (`model_hooks.install_*`), and once more with the
+    decode forward replayed as a CUDA graph (`install_cuda_graph_decode`; in overlap mode the graph is captured and
+    replayed on the worker thread's side stream).
 """
 import json
 import os
@@ -192,7 +194,8 @@ def test_unchanged_stack_on_dropins_matches_pure_reference(name, mode):
     ref = ref_stack.build(None, cfg, "cuda", torch.bfloat16, **POOL)
     ref_runs = _run(ref, prompts, mode)
     ref_ids = [r[0] for r in ref_runs]
-    for label, hooks in (("dropin", ()), ("dropin+K5K6K7", ("rope", "sampler", "prep"))):
+    for label, hooks in (("dropin", ()), ("dropin+K5K6K7", ("rope", "sampler", "prep")),
+                         ("dropin+K5K6K7+graph", ("rope", "sampler", "prep", "graph"))):
         got = ref_stack.build(DROPIN_DIR, cfg, "cuda", torch.bfloat16, **POOL, listen=False, hooks=hooks)
         assert type(got.scheduler.token_to_kv_pool).__module__ == "memory_pool"
         assert got.stack.attn_backend.__file__.startswith(DROPIN_DIR)
