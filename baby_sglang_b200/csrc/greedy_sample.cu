@@ -6,54 +6,61 @@
 //   * enforce_repetition_penalty_: for every DISTINCT previous token id,
 //       logit = logit > 0 ? logit / penalty : logit * penalty  (in the logits' dtype)   sample.py:19-36
 //   * torch.argmax over the vocabulary (first index among equal maxima; NaN counts as maximal)  sample.py:59-60
-// One CTA per request streams its vocabulary row once (16-byte loads); previous ids are marked in a
-// shared-memory bitmap so the penalty is applied on the fly; a block reduction picks (max, lowest index).
+// A thread-block cluster of up to 8 CTAs per request streams the vocabulary row once (16-byte loads, four in
+// flight per thread); previous ids are marked in a shared-memory bitmap (each CTA its own slice) so the penalty
+// is applied on the fly; warp -> block -> cluster (distributed shared memory) reduction picks (max, lowest index).
 // HBM-bound: bytes = B * V * e  (+ 8 B per previous id).  Integer output: bit-exact.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace bsgl {
 
-constexpr int kSampleThreads = 512;
+constexpr int kSampleThreads = 256;
+constexpr int kSampleMaxSplits = 8;   // portable cluster size
+
+// 16-byte streaming load: every logit is read exactly once
+__device__ __forceinline__ uint4 ld_stream16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
 
 template <typename T>
 struct LogitIo;
 template <>
 struct LogitIo<float> {
   static constexpr int kVec = 4;
-  static __device__ __forceinline__ void load(const float* p, float (&v)[8], int& n) {
-    const float4 a = *reinterpret_cast<const float4*>(p);
-    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
-    n = 4;
+  static __device__ __forceinline__ void unpack(const uint4& a, float (&v)[8]) {
+    v[0] = __uint_as_float(a.x); v[1] = __uint_as_float(a.y); v[2] = __uint_as_float(a.z); v[3] = __uint_as_float(a.w);
   }
   static __device__ __forceinline__ float round(float x) { return x; }
 };
 template <>
 struct LogitIo<__nv_bfloat16> {
   static constexpr int kVec = 8;
-  static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&v)[8], int& n) {
-    const uint4 a = *reinterpret_cast<const uint4*>(p);
+  static __device__ __forceinline__ void unpack(const uint4& a, float (&v)[8]) {
     const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&a);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const float2 f = __bfloat1622float2(h[i]);
       v[2 * i] = f.x; v[2 * i + 1] = f.y;
     }
-    n = 8;
   }
   static __device__ __forceinline__ float round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
 };
 template <>
 struct LogitIo<__half> {
   static constexpr int kVec = 8;
-  static __device__ __forceinline__ void load(const __half* p, float (&v)[8], int& n) {
-    const uint4 a = *reinterpret_cast<const uint4*>(p);
+  static __device__ __forceinline__ void unpack(const uint4& a, float (&v)[8]) {
     const __half2* h = reinterpret_cast<const __half2*>(&a);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const float2 f = __half22float2(h[i]);
       v[2 * i] = f.x; v[2 * i + 1] = f.y;
     }
-    n = 8;
   }
   static __device__ __forceinline__ float round(float x) { return __half2float(__float2half_rn(x)); }
 };
@@ -71,11 +78,19 @@ __global__ void __launch_bounds__(kSampleThreads) greedy_sample_kernel(
     const T* __restrict__ logits, int64_t row_stride, int vocab, const int32_t* __restrict__ qo_indptr,
     const int64_t* __restrict__ prev_ids, const int32_t* __restrict__ prev_indptr,
     const float* __restrict__ penalties, int64_t* __restrict__ next_ids) {
-  extern __shared__ uint32_t bitmap[];                       // ceil(vocab / 32) words, then reduction scratch
-  const int r = blockIdx.x;
+  extern __shared__ uint32_t bitmap[];                       // this CTA's slice of the previous-id bitmap
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int splits = (int)gridDim.x;                         // == cluster size: the CTAs of one vocabulary row
+  const int part = (int)blockIdx.x;                          // == rank in the cluster
+  const int r = blockIdx.y;
   const int64_t row = qo_indptr ? (int64_t)qo_indptr[r + 1] - 1 : r;   // last token of the request
   const T* src = logits + row * row_stride;
-  const int words = (vocab + 31) >> 5;
+  constexpr int VEC = LogitIo<T>::kVec;
+  // slice [e_lo, e_hi) of the row, a whole number of 16-byte vectors except for the row's tail
+  const int n_vec = (vocab + VEC - 1) / VEC;
+  const int per = (n_vec + splits - 1) / splits;
+  const int e_lo = min(vocab, part * per * VEC), e_hi = min(vocab, (part + 1) * per * VEC);
   float penalty = 1.f;
   int np = 0;
   if (prev_ids != nullptr) {
@@ -85,22 +100,21 @@ __global__ void __launch_bounds__(kSampleThreads) greedy_sample_kernel(
   // sample.py:22-31: nothing happens for penalty <= 1 (or NaN) or an empty history
   const bool penalise = penalty > 1.f && np > 0;
   const float inv_penalty = 1.f / penalty;
+  const int w0 = e_lo >> 5, words = ((e_hi + 31) >> 5) - w0;
   if (penalise) {
     for (int w = threadIdx.x; w < words; w += kSampleThreads) bitmap[w] = 0;
     __syncthreads();
     const int64_t* ids = prev_ids + prev_indptr[r];
     for (int i = threadIdx.x; i < np; i += kSampleThreads) {
       const int64_t t = ids[i];
-      if (t >= 0 && t < vocab) atomicOr(&bitmap[t >> 5], 1u << (t & 31));
+      if (t >= e_lo && t < e_hi) atomicOr(&bitmap[(int)(t >> 5) - w0], 1u << (t & 31));
     }
     __syncthreads();
   }
   float best = -INFINITY;
   int best_i = 0x7fffffff;
-  constexpr int VEC = LogitIo<T>::kVec;
-  const int n_vec = vocab / VEC;
   auto consider = [&](float v, int idx) {
-    if (penalise && (bitmap[idx >> 5] >> (idx & 31) & 1u))
+    if (penalise && (bitmap[(idx >> 5) - w0] >> (idx & 31) & 1u))
       // sample.py:34-35, in the logits' dtype.  torch's CUDA true-division by a Python scalar multiplies by
       // the fp32 reciprocal (BinaryDivTrueKernel.cu), which is what the reference executes on a GPU.
       v = LogitIo<T>::round(v > 0.f ? v * inv_penalty : v * penalty);
@@ -108,18 +122,32 @@ __global__ void __launch_bounds__(kSampleThreads) greedy_sample_kernel(
   };
   const bool aligned = ((uintptr_t)src % 16) == 0;
   if (aligned) {
-    for (int c = threadIdx.x; c < n_vec; c += kSampleThreads) {
-      float v[8];
-      int n;
-      LogitIo<T>::load(src + (int64_t)c * VEC, v, n);
+    // four independent 16-byte loads per thread in flight before any of them is compared
+    constexpr int U = 4;
+    const int c_lo = e_lo / VEC, c_hi = e_hi / VEC;          // whole vectors of the slice
+    for (int c0 = c_lo + threadIdx.x; c0 < c_hi; c0 += U * kSampleThreads) {
+      uint4 raw[U];
 #pragma unroll
-      for (int i = 0; i < VEC; ++i) consider(v[i], c * VEC + i);
+      for (int u = 0; u < U; ++u) {
+        const int c = c0 + u * kSampleThreads;
+        raw[u] = c < c_hi ? ld_stream16(src + (int64_t)c * VEC) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int c = c0 + u * kSampleThreads;
+        if (c < c_hi) {
+          float v[8];
+          LogitIo<T>::unpack(raw[u], v);
+#pragma unroll
+          for (int i = 0; i < VEC; ++i) consider(v[i], c * VEC + i);
+        }
+      }
     }
-    for (int idx = n_vec * VEC + threadIdx.x; idx < vocab; idx += kSampleThreads) consider((float)src[idx], idx);
+    for (int idx = c_hi * VEC + threadIdx.x; idx < e_hi; idx += kSampleThreads) consider((float)src[idx], idx);
   } else {
-    for (int idx = threadIdx.x; idx < vocab; idx += kSampleThreads) consider((float)src[idx], idx);
+    for (int idx = e_lo + threadIdx.x; idx < e_hi; idx += kSampleThreads) consider((float)src[idx], idx);
   }
-  // warp, then block reduction
+  // warp, then block, then cluster reduction (a total order: the result does not depend on the split)
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, best, o);
@@ -128,6 +156,8 @@ __global__ void __launch_bounds__(kSampleThreads) greedy_sample_kernel(
   }
   __shared__ float wv[kSampleThreads / 32];
   __shared__ int wi[kSampleThreads / 32];
+  __shared__ float cv[kSampleMaxSplits];                     // rank 0's copy collects one candidate per CTA
+  __shared__ int ci[kSampleMaxSplits];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane == 0) { wv[warp] = best; wi[warp] = best_i; }
   __syncthreads();
@@ -140,7 +170,18 @@ __global__ void __launch_bounds__(kSampleThreads) greedy_sample_kernel(
       const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
       if (better(ov, oi, best, best_i)) { best = ov; best_i = oi; }
     }
-    if (lane == 0) next_ids[r] = best_i;
+    if (lane == 0) {
+      cluster.map_shared_rank(cv, 0)[part] = best;           // distributed shared memory of the row's first CTA
+      cluster.map_shared_rank(ci, 0)[part] = best_i;
+    }
+  }
+  cluster.sync();
+  if (part == 0 && threadIdx.x == 0) {
+    best = cv[0];
+    best_i = ci[0];
+    for (int s = 1; s < splits; ++s)
+      if (better(cv[s], ci[s], best, best_i)) { best = cv[s]; best_i = ci[s]; }
+    next_ids[r] = best_i;
   }
 }
 
@@ -158,20 +199,40 @@ extern "C" int bsgl_greedy_sample(const void* logits, int64_t row_stride, int vo
   BSGL_REQUIRE((prev_ids == nullptr) == (prev_indptr == nullptr) && (prev_ids == nullptr) == (penalties == nullptr),
                "bsgl_greedy_sample: prev_ids, prev_indptr and penalties go together");
   BSGL_REQUIRE(dtype == BSGL_BF16 || dtype == BSGL_F16 || dtype == BSGL_F32, "bsgl_greedy_sample: bad dtype");
-  const size_t smem = prev_ids ? (size_t)((vocab + 31) / 32) * 4 : 0;
+  // A vocabulary row is split over a thread-block cluster so that the grid fills the machine (8 CTAs of 256
+  // threads per SM) even at small batch; the cluster's candidates meet in the first CTA's shared memory.
+  int sms = 148, dev = 0;
+  BSGL_CUDA_TRY(cudaGetDevice(&dev));
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  int splits = sms * 8 / batch;
+  splits = splits < 1 ? 1 : (splits > kSampleMaxSplits ? kSampleMaxSplits : splits);
+  const int vec = dtype == BSGL_F32 ? 4 : 8;
+  const int per = ((vocab + vec - 1) / vec + splits - 1) / splits * vec;   // elements per slice
+  const size_t smem = prev_ids ? (size_t)(per / 32 + 2) * 4 : 0;
+  BSGL_REQUIRE(batch <= 65535, "bsgl_greedy_sample: batch %d > 65535", batch);
   cudaStream_t s = (cudaStream_t)stream;
 #define BSGL_GS(T)                                                                                          \
   do {                                                                                                      \
     static thread_local int configured_dev = -1;                                                            \
-    int dev = 0;                                                                                            \
-    BSGL_CUDA_TRY(cudaGetDevice(&dev));                                                                     \
     if (configured_dev != dev) {                                                                            \
       BSGL_CUDA_TRY(cudaFuncSetAttribute(greedy_sample_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                         (1 << 20) / 8));                                                   \
+                                         (1 << 20) / 8 + 8));                                               \
       configured_dev = dev;                                                                                 \
     }                                                                                                       \
-    greedy_sample_kernel<T><<<(unsigned)batch, kSampleThreads, smem, s>>>(                                  \
-        (const T*)logits, row_stride, vocab, qo_indptr, prev_ids, prev_indptr, penalties, next_ids);        \
+    cudaLaunchConfig_t cfg = {};                                                                            \
+    cfg.gridDim = dim3((unsigned)splits, (unsigned)batch);                                                  \
+    cfg.blockDim = dim3(kSampleThreads);                                                                    \
+    cfg.dynamicSmemBytes = smem;                                                                            \
+    cfg.stream = s;                                                                                         \
+    cudaLaunchAttribute attr[1];                                                                            \
+    attr[0].id = cudaLaunchAttributeClusterDimension;                                                       \
+    attr[0].val.clusterDim.x = (unsigned)splits;                                                            \
+    attr[0].val.clusterDim.y = 1;                                                                           \
+    attr[0].val.clusterDim.z = 1;                                                                           \
+    cfg.attrs = attr;                                                                                       \
+    cfg.numAttrs = 1;                                                                                       \
+    BSGL_CUDA_TRY(cudaLaunchKernelEx(&cfg, greedy_sample_kernel<T>, (const T*)logits, row_stride, vocab,    \
+                                     qo_indptr, prev_ids, prev_indptr, penalties, next_ids));               \
     return check_launch("greedy_sample_kernel");                                                            \
   } while (0)
   if (dtype == BSGL_BF16) BSGL_GS(__nv_bfloat16);

@@ -2,8 +2,8 @@
 // Replaces MHATokenToKVPool.set_kv_buffer (reference memory_pool.py:152-171): int32 loc -> int64
 // widen (:159-160), optional cast to the pool dtype (:163-165), two index-puts (:170-171).
 //
-// HBM-bound byte work: every thread moves one 16-byte chunk of a destination row with one vector
-// load and one vector store (two loads when narrowing from fp32); grid-stride, grid = SMs x 8.
+// HBM-bound byte work: every thread moves one 16-byte chunk of a token's K row and the same chunk of its V
+// row (two vector loads, two vector stores; twice the loads when narrowing from fp32), one thread per chunk.
 // Algorithmic bytes: 2 * (2 * T * Hkv * D * e) + 4 * T.
 #include "common.cuh"
 
@@ -76,36 +76,32 @@ __global__ void __launch_bounds__(256) kv_store_kernel(DstT* __restrict__ k_slab
   asm volatile("griddepcontrol.launch_dependents;");
   const int chunks_per_head = head_dim >> 3;                 // 8 elements (16 B of 16-bit dst) per chunk
   const int chunks_per_row = n_kv_heads * chunks_per_head;   // per K (or V) row
-  const int64_t total = n_tokens * 2 * chunks_per_row;
   const int64_t slab_row = (int64_t)n_kv_heads * head_dim;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t t = i / (2 * chunks_per_row);
-    int c = (int)(i - t * 2 * chunks_per_row);
-    const bool is_v = c >= chunks_per_row;
-    if (is_v) c -= chunks_per_row;
-    const int h = c / chunks_per_head;
-    const int d = (c - h * chunks_per_head) << 3;
-    const int64_t slot = (int64_t)loc[t];                    // int32 -> int64 widen
-    if ((uint64_t)slot >= (uint64_t)n_slots) __trap();       // the reference's index-put device-asserts here
-    const SrcT* src = is_v ? v_src + t * v_row_stride + h * v_head_stride + d
-                           : k_src + t * k_row_stride + h * k_head_stride + d;
-    DstT* dst = (is_v ? v_slab : k_slab) + slot * slab_row + (int64_t)h * head_dim + d;
-    *reinterpret_cast<uint4*>(dst) = Cvt8<SrcT, DstT>::load(src);
-  }
+  // One thread = the same 16-byte chunk of a token's K row and V row: both source loads are issued before
+  // the dependent slot load is consumed, and a CTA's 256 threads cover whole rows with coalesced 16-byte
+  // accesses.  No loop: the grid covers every chunk (T x chunks_per_row <= 2^31 is checked by the launcher).
+  const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+  const uint32_t t = i / (uint32_t)chunks_per_row;
+  if ((int64_t)t >= n_tokens) return;
+  const int c = (int)(i - t * (uint32_t)chunks_per_row);
+  const int h = c / chunks_per_head;
+  const int d = (c - h * chunks_per_head) << 3;
+  const uint4 kq = Cvt8<SrcT, DstT>::load(k_src + (int64_t)t * k_row_stride + h * k_head_stride + d);
+  const uint4 vq = Cvt8<SrcT, DstT>::load(v_src + (int64_t)t * v_row_stride + h * v_head_stride + d);
+  const int64_t slot = (int64_t)loc[t];                      // int32 -> int64 widen
+  if ((uint64_t)slot >= (uint64_t)n_slots) __trap();         // the reference's index-put device-asserts here
+  const int64_t off = slot * slab_row + (int64_t)h * head_dim + d;
+  *reinterpret_cast<uint4*>(k_slab + off) = kq;
+  *reinterpret_cast<uint4*>(v_slab + off) = vq;
 }
 
 template <typename SrcT, typename DstT>
 static int launch_kv_store(void* k_slab, void* v_slab, int64_t n_slots, const int32_t* loc, const void* k_src, const void* v_src,
                            int64_t n_tokens, int n_kv_heads, int head_dim, int64_t krs, int64_t khs, int64_t vrs,
                            int64_t vhs, cudaStream_t stream) {
-  const int64_t total = n_tokens * 2 * n_kv_heads * (head_dim >> 3);
-  int sms = 148;
-  int dev = 0;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  int64_t blocks = (total + 255) / 256;
-  if (blocks > (int64_t)sms * 8) blocks = (int64_t)sms * 8;
+  const int64_t total = n_tokens * n_kv_heads * (head_dim >> 3);   // (token, 16-byte chunk) pairs
+  BSGL_REQUIRE(total < (1ll << 31), "bsgl_kv_store: %lld row chunks in one call (limit 2^31)", (long long)total);
+  const int64_t blocks = (total + 255) / 256;
   kv_store_kernel<SrcT, DstT><<<(unsigned)blocks, 256, 0, stream>>>(
       (DstT*)k_slab, (DstT*)v_slab, n_slots, loc, (const SrcT*)k_src, (const SrcT*)v_src, n_tokens, n_kv_heads, head_dim, krs,
       khs, vrs, vhs);

@@ -41,9 +41,9 @@ __device__ __forceinline__ float2 unpack2<__half>(uint32_t v) {
   return __half22float2(*reinterpret_cast<__half2*>(&v));
 }
 
-// One CTA per token.  cos/sin of the token (D/2 values each, already rounded to T) are computed
-// once into shared memory; then every thread rotates 16-byte chunk pairs (x1 chunk c, x2 chunk c)
-// of the q and k heads and copies the v chunks.
+// One CTA per token.  Every thread first issues the loads of its 16-byte chunk pairs (x1 chunk c, x2 chunk c
+// of a q or k head) and v chunks; cos/sin of the token (D/2 values each, already rounded to T) are computed
+// once into shared memory while those are in flight; then the pairs are rotated and stored.
 template <typename T>
 __global__ void __launch_bounds__(kRopeThreads) rope_kv_store_kernel(
     const T* __restrict__ qkv, int64_t row_stride, const int64_t* __restrict__ positions,
@@ -53,6 +53,29 @@ __global__ void __launch_bounds__(kRopeThreads) rope_kv_store_kernel(
   asm volatile("griddepcontrol.launch_dependents;");   // the attention kernel may launch and set up meanwhile
   const int half = head_dim >> 1;
   const int64_t t = blockIdx.x;
+  const T* row = qkv + t * row_stride;
+  const int cph = half >> 3;                     // chunk pairs per rotated head
+  const int n_rot = (n_q_heads + n_kv_heads) * cph;
+  const int n_v = n_kv_heads * (head_dim >> 3);
+  const int n_work = n_rot + n_v;
+  const int64_t slab_row = (int64_t)n_kv_heads * head_dim;
+  // work item w < n_rot: chunk pair (x1 chunk, x2 chunk) of a q or k head; else a 16-byte chunk of the V row
+  auto fetch = [&](int w, uint4& a, uint4& b) {
+    if (w < n_rot) {
+      const int hd = w / cph;                    // head among q heads then k heads
+      const int c = (w - hd * cph) << 3;         // first element of the chunk inside each half
+      const T* src = row + (int64_t)hd * head_dim + c;
+      a = *reinterpret_cast<const uint4*>(src);          // x1[c..c+7]
+      b = *reinterpret_cast<const uint4*>(src + half);   // x2[c..c+7]
+    } else if (w < n_work) {
+      a = *reinterpret_cast<const uint4*>(row + (int64_t)(n_q_heads + n_kv_heads) * head_dim + ((w - n_rot) << 3));
+    }
+  };
+  // The first two work items of every thread (one whole 7B row) are in flight while cos/sin are evaluated.
+  uint4 a0, b0, a1, b1;
+  fetch(threadIdx.x, a0, b0);
+  fetch(threadIdx.x + kRopeThreads, a1, b1);
+  const int64_t slot = loc ? (int64_t)loc[t] : 0;
   const float pos = (float)positions[t];         // positions.float()
   for (int i = threadIdx.x; i < half; i += kRopeThreads) {
     const float f = pos * inv_freq[i];           // torch.outer in fp32
@@ -60,20 +83,11 @@ __global__ void __launch_bounds__(kRopeThreads) rope_kv_store_kernel(
     cs[half + i] = rnd<T>(sinf(f));
   }
   __syncthreads();
-  const T* row = qkv + t * row_stride;
-  const int64_t slot = loc ? (int64_t)loc[t] : 0;
   if (loc && (uint64_t)slot >= (uint64_t)n_slots) __trap();   // the reference's index-put device-asserts here
-  const int cph = half >> 3;                     // chunk pairs per rotated head
-  const int n_rot = (n_q_heads + n_kv_heads) * cph;
-  const int n_v = n_kv_heads * (head_dim >> 3);
-  const int64_t slab_row = (int64_t)n_kv_heads * head_dim;
-  for (int w = threadIdx.x; w < n_rot + n_v; w += kRopeThreads) {
+  auto finish = [&](int w, const uint4& a, const uint4& b) {
     if (w < n_rot) {
-      const int hd = w / cph;                    // head among q heads then k heads
-      const int c = (w - hd * cph) << 3;         // first element of the chunk inside each half
-      const T* src = row + (int64_t)hd * head_dim + c;
-      const uint4 a = *reinterpret_cast<const uint4*>(src);          // x1[c..c+7]
-      const uint4 b = *reinterpret_cast<const uint4*>(src + half);   // x2[c..c+7]
+      const int hd = w / cph;
+      const int c = (w - hd * cph) << 3;
       const uint32_t* au = &a.x;
       const uint32_t* bu = &b.x;
       uint4 o1, o2;
@@ -96,16 +110,22 @@ __global__ void __launch_bounds__(kRopeThreads) rope_kv_store_kernel(
       if (hd < n_q_heads) {
         dst = q_out + (t * n_q_heads + hd) * head_dim + c;
       } else {
-        if (k_slab == nullptr) continue;
+        if (k_slab == nullptr) return;
         dst = k_slab + slot * slab_row + (int64_t)(hd - n_q_heads) * head_dim + c;
       }
       *reinterpret_cast<uint4*>(dst) = o1;
       *reinterpret_cast<uint4*>(dst + half) = o2;
-    } else if (v_slab != nullptr) {
-      const int e = (w - n_rot) << 3;            // element inside the V row
-      const uint4 v = *reinterpret_cast<const uint4*>(row + (int64_t)(n_q_heads + n_kv_heads) * head_dim + e);
-      *reinterpret_cast<uint4*>(v_slab + slot * slab_row + e) = v;
+    } else if (w < n_work && v_slab != nullptr) {
+      *reinterpret_cast<uint4*>(v_slab + slot * slab_row + ((w - n_rot) << 3)) = a;
     }
+  };
+  finish(threadIdx.x, a0, b0);
+  finish(threadIdx.x + kRopeThreads, a1, b1);
+  for (int w = threadIdx.x + 2 * kRopeThreads; w < n_work; w += 2 * kRopeThreads) {   // wider rows than 512 items
+    fetch(w, a0, b0);
+    fetch(w + kRopeThreads, a1, b1);
+    finish(w, a0, b0);
+    finish(w + kRopeThreads, a1, b1);
   }
 }
 

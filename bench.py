@@ -565,51 +565,60 @@ def measure_small_kernels(device):
     dt = torch.bfloat16
     out = {}
 
-    def timeit(fn, reps=30, flush=None):
-        for _ in range(3):
+    def timeit(fns, trains=7, per_train=24):
+        """Median over `trains` of (CUDA-event time of `per_train` back-to-back launches) / per_train.  The launches
+        rotate over `fns`: distinct input sets whose total footprint exceeds 2 x L2, so every launch reads its
+        inputs from HBM and no foreign dirty lines are written back on its clock (zeroing a flush buffer between
+        launches, as round 1 did, leaves 126 MB of dirty L2 lines for the timed kernel to evict)."""
+        for fn in fns:
             fn()
         torch.cuda.synchronize()
         ts = []
-        for _ in range(reps):
-            if flush is not None:
-                flush.zero_()                # > L2: evicts the kernel's inputs between timed launches
+        for _ in range(trains):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            fn()
+            for i in range(per_train):
+                fns[i % len(fns)]()
             b.record()
             torch.cuda.synchronize()
-            ts.append(a.elapsed_time(b))
+            ts.append(a.elapsed_time(b) / per_train)
         return statistics.median(ts)
 
-    flush = torch.empty(512 << 20, dtype=torch.uint8, device=device)
+    NSET = 4
     for T in (256, 16384):
         S = 1 << 20
         ks = torch.empty(S + 1, Hkv, D, device=device, dtype=dt)
         vs = torch.empty(S + 1, Hkv, D, device=device, dtype=dt)
-        loc = (torch.randperm(S, device=device)[:T] + 1).to(torch.int32)
-        qkv = torch.randn(T, (Hq + 2 * Hkv) * D, device=device, dtype=dt)
-        q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
-        k, v = k.contiguous().view(T, Hkv, D), v.view(T, Hkv, D)
-        ms = timeit(lambda: ops.kv_store(ks, vs, loc, k, v), flush=flush)
+        inv = 1.0 / (1e6 ** (torch.arange(0, D, 2, device=device).float() / D))
+        k1, k5 = [], []
+        for i in range(NSET):
+            loc = (torch.randperm(S, device=device)[:T] + 1).to(torch.int32)
+            qkv = torch.randn(T, (Hq + 2 * Hkv) * D, device=device, dtype=dt)
+            q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+            k, v = k.contiguous().view(T, Hkv, D), v.view(T, Hkv, D)
+            pos = torch.randint(0, 4096, (T,), device=device)
+            k1.append(lambda loc=loc, k=k, v=v: ops.kv_store(ks, vs, loc, k, v))
+            k5.append(lambda qkv=qkv, pos=pos, loc=loc: ops.rope_kv_store(qkv, pos, inv, Hq, Hkv, D, ks, vs, loc))
+        ms = timeit(k1)
         nb = kv_store_bytes(T, Hkv, D)
         out[f"K1_kv_store_T{T}"] = {"bytes": nb, "us": round(ms * 1e3, 2), "GBps": round(nb / ms / 1e6, 1),
                                     "frac_of_hbm_peak": round(nb / ms / 1e6 / peak, 4)}
-        pos = torch.randint(0, 4096, (T,), device=device)
-        inv = 1.0 / (1e6 ** (torch.arange(0, D, 2, device=device).float() / D))
-        ms = timeit(lambda: ops.rope_kv_store(qkv, pos, inv, Hq, Hkv, D, ks, vs, loc), flush=flush)
+        ms = timeit(k5)
         nb = 2 * T * (Hq + 2 * Hkv) * D * 2 + 12 * T
         out[f"K5_rope_kv_store_T{T}"] = {"bytes": nb, "us": round(ms * 1e3, 2), "GBps": round(nb / ms / 1e6, 1),
                                          "frac_of_hbm_peak": round(nb / ms / 1e6 / peak, 4)}
-        del ks, vs, qkv
-    logits = torch.randn(256, vocab, device=device, dtype=dt)
-    ms = timeit(lambda: ops.greedy_sample(logits), flush=flush)
-    nb = logits.numel() * 2 + 8 * 256
+        del ks, vs, k1, k5, qkv, q, k, v
+        _free()
+    logits = [torch.randn(256, vocab, device=device, dtype=dt) for _ in range(NSET)]
+    ms = timeit([lambda x=x: ops.greedy_sample(x) for x in logits])
+    nb = logits[0].numel() * 2 + 8 * 256
     out["K6_greedy_sample_B256"] = {"bytes": nb, "us": round(ms * 1e3, 2), "GBps": round(nb / ms / 1e6, 1),
                                     "frac_of_hbm_peak": round(nb / ms / 1e6 / peak, 4)}
-    out["note"] = ("CUDA events per launch, median of 30, a 512 MiB buffer zeroed between launches (inputs evicted "
-                   "from L2); bytes = SURVEY §8d formulas (K1: 2*(2*T*Hkv*D*e)+4T; K5: read + write of the fused "
-                   "row; K6: B*V*e).  At T=256 these are launch-latency bound (a few us of work).")
-    del flush, logits
+    out["note"] = ("CUDA events around trains of 24 back-to-back launches rotating over 4 distinct input sets (total "
+                   "footprint > 2 x L2, no flush writes), median of 7 trains, per launch; bytes = SURVEY §8d formulas "
+                   "(K1: 2*(2*T*Hkv*D*e)+4T; K5: read + write of the fused row; K6: B*V*e).  At T=256 these are "
+                   "launch-latency bound (a few us of work).")
+    del logits
     _free()
     return out
 
