@@ -10,8 +10,8 @@
 //            into a double-buffered TMEM accumulator, and the epilogue warps push each finished 128x128
 //            tile as bf16 straight from registers into the OWNER rank's staging buffer over NVLink
 //            (peer-mapped memory, 512-byte coalesced bursts), then publish a per-(tile, source) flag with a
-//            system-scope release.  Tiles are visited owner-by-owner starting at rank+1, so every link is
-//            busy from the first tile on and a rank's own tiles come last.
+//            system-scope release.  Every rank visits the tiles in the same order: the partials of a tile reach
+//            its owner together, the 148 tiles in flight per rank spread over all owners and links.
 //   phase 2  the owner of a tile (tile % world) waits for its `world` partials, adds them in fp32 in rank
 //            order (the result is bit-identical everywhere because only the owner computes it), rounds once
 //            to bf16 and stores the final tile into EVERY rank's output buffer, then raises that tile's
@@ -39,6 +39,7 @@
 // Bound: NVLink/NVSwitch bandwidth.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -214,7 +215,7 @@ template <typename T>
 __global__ void __launch_bounds__(kOpThreads, 1)
 oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                        const __grid_constant__ OprojComm comm, int M, int N, int K, int rank, int world, int max_slots,
-                       int max_tiles, uint64_t timeout_ns) {
+                       int max_tiles, uint64_t timeout_ns, int grouped_order) {
   extern __shared__ uint8_t smem_dyn[];
   const uint32_t raw = smem_u32(smem_dyn);
   const uint32_t base = (raw + 1023u) & ~1023u;          // SWIZZLE_128B tiles need 1024-byte alignment
@@ -263,7 +264,7 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
       tma_prefetch_desc(&tm_b);
       uint32_t it = 0;
       for (int i = blockIdx.x; i < n_tiles; i += gridDim.x) {
-        const int tile = nvls ? i : tile_at(i, n_tiles, rank, world);
+        const int tile = (nvls || !grouped_order) ? i : tile_at(i, n_tiles, rank, world);
         const int m0 = (tile / n_nt) * kOpBM, n0 = (tile % n_nt) * kOpBN;
         for (int kb = 0; kb < n_kb; ++kb, ++it) {
           const uint32_t s = it % kOpStages, ph = (it / kOpStages) & 1u;
@@ -307,7 +308,7 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     uint32_t tcount = 0;
     for (int i = blockIdx.x; i < n_tiles; i += gridDim.x, ++tcount) {
-      const int tile = nvls ? i : tile_at(i, n_tiles, rank, world);
+      const int tile = (nvls || !grouped_order) ? i : tile_at(i, n_tiles, rank, world);
       const int owner = tile % world, slot = tile / world;
       const uint32_t buf = tcount & 1u;
       mbar_wait_guarded(accf0 + 8 * buf, (tcount >> 1) & 1u);
@@ -477,8 +478,16 @@ static int launch_oproj(const CUtensorMap& ta, const CUtensorMap& tb, const Opro
   // every CTA must be resident: phase 2 waits on tiles other CTAs of this grid produce (one CTA per SM: 197 KB of
   // shared memory each; a persistent kernel of another stream holding SMs would stall it until the timeout)
   const int grid = n_tiles < sms ? n_tiles : sms;
+  // Visiting order of the peer-store path.  "global" (default): every rank walks the tiles in the same order, so
+  // the `world` partials of a tile reach its owner at about the same time and the owner's reduction trails the
+  // GEMM tile by tile (the 148 tiles in flight cover all owners evenly: no hot link).  "grouped": owner by owner
+  // starting at rank + 1 (round 1's order; an owner's tiles then all complete in the last 1/world of the GEMM).
+  static const int grouped = [] {
+    const char* e = getenv("BSGL_K8_TILE_ORDER");
+    return (e && e[0] == 'g' && e[1] == 'r') ? 1 : 0;
+  }();
   kern<<<grid, kOpThreads, kOpSmemBytes, stream>>>(ta, tb, comm, M, N, K, rank, world, max_slots, max_tiles,
-                                                   timeout_ns);
+                                                   timeout_ns, grouped);
   return check_launch("oproj_allreduce_kernel");
 }
 

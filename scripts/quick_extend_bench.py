@@ -60,7 +60,14 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--mode", default="tcgen05", choices=["tcgen05", "rowwise"])
     ap.add_argument("--no-order", action="store_true", help="dispatch requests in index order (no heavy-first)")
+    ap.add_argument("--sustain", type=float, default=0.0,
+                    help="also launch back to back for this many seconds while nvidia-smi samples SM clock and power")
+    ap.add_argument("--lib", default=None, help="load this build of the library instead of the in-tree one "
+                                                "(e.g. one compiled with -DBSGL_EXT_EXPERIMENTS)")
     a = ap.parse_args()
+    if a.lib:
+        from baby_sglang_b200 import _lib
+        _lib.LIB_PATH = os.path.abspath(a.lib)
     w = build(a.geom, a.batch, a.max_prefix, a.ext, fixed_prefix=a.fixed_prefix)
     dev = w["q"].device
     seq, pre = w["seq"].to(dev), w["prefix"].to(dev)
@@ -89,11 +96,39 @@ def main():
     ms.sort()
     med = ms[len(ms) // 2]
     fl = extend_flops(w["Hq"], w["D"], w["prefix"].tolist(), w["ext"].tolist())
+    sustained = None
+    if a.sustain > 0:
+        import subprocess
+        import time
+        smi = subprocess.Popen(["nvidia-smi", "-i", "0", "--query-gpu=clocks.sm,power.draw,power.limit,"
+                                "clocks_event_reasons.sw_power_cap", "--format=csv,noheader,nounits", "-lms", "100"],
+                               stdout=subprocess.PIPE, text=True)
+        time.sleep(0.3)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n, t0 = 0, time.time()
+        e0.record()
+        while time.time() - t0 < a.sustain:
+            for _ in range(50):
+                run()
+            n += 50
+            torch.cuda.synchronize()
+        e1.record()
+        torch.cuda.synchronize()
+        smi.terminate()
+        rows = [[x.strip() for x in ln.split(",")] for ln in smi.stdout.read().strip().splitlines()]
+        rows = [r for r in rows if len(r) == 4][3:]
+        clk = sorted(float(r[0]) for r in rows)
+        pw = sorted(float(r[1]) for r in rows)
+        sustained = {"launches": n, "ms_avg": round(e0.elapsed_time(e1) / n, 4),
+                     "TFLOPs": round(fl / (e0.elapsed_time(e1) / n) / 1e9, 1),
+                     "sm_mhz_median": clk[len(clk) // 2] if clk else None, "power_w_median": pw[len(pw) // 2] if pw else None,
+                     "power_limit_w": float(rows[0][2]) if rows else None,
+                     "power_cap_active_share": round(sum(r[3].lower().startswith("active") for r in rows) / max(1, len(rows)), 2)}
     print(json.dumps({"geom": a.geom, "batch": a.batch, "ext": a.ext, "mode": a.mode,
                       "prefix": "fixed %d" % a.fixed_prefix if a.fixed_prefix is not None else "U[0,%d]" % a.max_prefix,
                       "ms_med": round(med, 4), "ms_min": round(ms[0], 4), "TFLOPs_med": round(fl / med / 1e9, 1),
                       "TFLOPs_best": round(fl / ms[0] / 1e9, 1), "frac_of_1665.9": round(fl / med / 1e9 / 1665.9, 4),
-                      "flops": fl}))
+                      "flops": fl, "sustained": sustained, "expmode": os.environ.get("BSGL_EXT_EXPMODE")}))
 
 
 if __name__ == "__main__":

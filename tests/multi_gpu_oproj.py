@@ -23,9 +23,10 @@ sys.path.insert(0, DROPIN_DIR)
 import tp_runtime  # noqa: E402
 
 
-def main():
+def run(mode, rank, world, group):
+    """All cases under one exchange: "" = the communicator's default (peer stores), "nvls" = in-switch reduction."""
     bench = "--bench" in sys.argv
-    rank, world, group = tp_runtime.init_tp()
+    os.environ["BSGL_K8_EXCHANGE"] = mode
     dev = torch.device("cuda", torch.cuda.current_device())
     # (tokens, hidden, full K = Hq * D): 32B decode C5, a ragged token count, 7B geometry, a tiny batch
     cases = [(1024, 5120, 5120), (333, 5120, 5120), (256, 3584, 3584), (7, 1536, 1536)]
@@ -107,6 +108,14 @@ def main():
             print(json.dumps(line), flush=True)
     comm.close()
     dist.barrier(group=group)
+    return ok
+
+
+def main():
+    rank, world, group = tp_runtime.init_tp()
+    ok = run("", rank, world, group)
+    if world > 1:
+        ok &= run("nvls", rank, world, group)     # falls back to peer stores where multicast is unavailable
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 
