@@ -566,22 +566,32 @@ def measure_small_kernels(device):
     out = {}
 
     def timeit(fns, trains=7, per_train=24):
-        """Median over `trains` of (CUDA-event time of `per_train` back-to-back launches) / per_train.  The launches
-        rotate over `fns`: distinct input sets whose total footprint exceeds 2 x L2, so every launch reads its
-        inputs from HBM and no foreign dirty lines are written back on its clock (zeroing a flush buffer between
-        launches, as round 1 did, leaves 126 MB of dirty L2 lines for the timed kernel to evict)."""
+        """Median over `trains` replays of ONE CUDA graph holding `per_train` back-to-back launches, CUDA events
+        around the replay, per launch (a graph so that the host's ~10 us per Python call is not what is timed).
+        The launches rotate over `fns`: distinct input sets whose total footprint exceeds 2 x L2, so every launch
+        reads its inputs from HBM and no foreign dirty lines are written back on its clock (zeroing a flush buffer
+        between launches, as round 1 did, leaves 126 MB of dirty L2 lines for the timed kernel to evict)."""
         for fn in fns:
             fn()
+        torch.cuda.synchronize()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(graph, stream=side):
+                keep = [fns[i % len(fns)]() for i in range(per_train)]
+        torch.cuda.synchronize()
+        graph.replay()
         torch.cuda.synchronize()
         ts = []
         for _ in range(trains):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            for i in range(per_train):
-                fns[i % len(fns)]()
+            graph.replay()
             b.record()
             torch.cuda.synchronize()
             ts.append(a.elapsed_time(b) / per_train)
+        del graph, keep
         return statistics.median(ts)
 
     NSET = 4
@@ -614,8 +624,8 @@ def measure_small_kernels(device):
     nb = logits[0].numel() * 2 + 8 * 256
     out["K6_greedy_sample_B256"] = {"bytes": nb, "us": round(ms * 1e3, 2), "GBps": round(nb / ms / 1e6, 1),
                                     "frac_of_hbm_peak": round(nb / ms / 1e6 / peak, 4)}
-    out["note"] = ("CUDA events around trains of 24 back-to-back launches rotating over 4 distinct input sets (total "
-                   "footprint > 2 x L2, no flush writes), median of 7 trains, per launch; bytes = SURVEY §8d formulas "
+    out["note"] = ("CUDA events around replays of one CUDA graph of 24 back-to-back launches rotating over 4 distinct "
+                   "input sets (total footprint > 2 x L2, no flush writes, no host time), median of 7 replays, per launch; bytes = SURVEY §8d formulas "
                    "(K1: 2*(2*T*Hkv*D*e)+4T; K5: read + write of the fused row; K6: B*V*e).  At T=256 these are "
                    "launch-latency bound (a few us of work).")
     del logits
