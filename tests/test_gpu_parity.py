@@ -524,6 +524,38 @@ def test_greedy_sample_full_vocab_vs_oracle(ops, dtype):
     assert torch.equal(got2.cpu(), O.greedy_sample(dec, None, [[]] * B, [1.0] * B))
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("B,V", [(1, 152064), (7, 32000), (300, 151936), (3, 1000), (5, 50001)])
+def test_greedy_sample_register_path_edges(ops, dtype, B, V):
+    """The no-penalty 16-bit path (slice in registers, cluster-wide max then lowest index) against torch.argmax
+    semantics: exact ties, -0.0 vs +0.0, NaN of either sign (first NaN wins), rows of -inf, every cluster split,
+    and vocabularies that are not a multiple of 8 (which take the exact path)."""
+    g = torch.Generator().manual_seed(B * 1000 + V)
+    logits = (torch.randn(B, V, generator=g) * 3).to(dtype)
+    for i in range(B):
+        j = int(torch.argmax(logits[i].float()))
+        kind = i % 6
+        if kind == 0:                                  # tie at a lower and a higher index
+            logits[i, (j * 5 + 3) % V] = logits[i, j]
+        elif kind == 1:                                # NaN with the sign bit set, then a positive one later
+            logits[i, V // 3] = torch.tensor(float("nan"), dtype=dtype).view(torch.int16).bitwise_or(-32768).view(dtype)
+            logits[i, V // 2] = float("nan")
+        elif kind == 2:                                # the whole row -inf: index 0
+            logits[i] = float("-inf")
+        elif kind == 3:                                # maximum is zero: -0.0 first, +0.0 later -> first index
+            logits[i] = -logits[i].abs() - 1
+            logits[i, 11] = -0.0
+            logits[i, V - 1] = 0.0
+        elif kind == 4:                                # maximum in the very last element
+            logits[i, V - 1] = 100.0
+    want = O.greedy_sample(logits, None, [[]] * B, [1.0] * B)
+    got = ops.greedy_sample(logits.cuda())
+    assert torch.equal(got.cpu(), want)
+    for i in range(B):                                 # and the oracle itself against torch on the edge rows
+        if i % 6 in (2, 3):
+            assert int(want[i]) == int(torch.argmax(logits[i].float()))
+
+
 def test_batched_greedy_sampler_hook(ops):
     """`install_batched_greedy_sampler` on an object with the reference scheduler's method: greedy batches go
     through K6 (ids equal to the fixture the reference produced), other batches reach the original method."""
