@@ -142,13 +142,13 @@ class FusedOProjAllReduce:
     peer mapping and the NVSwitch MULTICAST mapping; `exchange = "nvls"`): partial tiles then stay in each rank's
     own staging and the tile's owner reduces them inside the switch (`multimem.ld_reduce`) and broadcasts the sum
     (`multimem.st`).  Without multicast support the buffers are cudaMalloc + CUDA IPC through the C ABI and
-    partial tiles travel by peer stores (`exchange = "peer-stores"`).  The choice is made PER CALL and defaults to
-    peer stores: measured on 4 and 8 B200s (profiles/r2_k8_trace_w4.jsonl, _w8.jsonl) neither exchange is
-    bandwidth-bound at these sizes -- both are chains of flag round trips -- and the in-switch chain (flag ->
-    multimem.ld_reduce -> multimem.st -> flag) is the longer one for large reductions (TP8, 10 MiB: 70.9 vs 60.1 us;
-    TP4: 71.5 vs 53.0 us), within +-3 us for small ones.  `BSGL_K8_EXCHANGE` = `nvls` (always in-switch), `nvls-small`
-    (in-switch below BSGL_K8_NVLS_MAX_BYTES, default 4 MiB, at world >= 8), `peer` (IPC buffers, peer stores only) or
-    `symm-peer` (symmetric memory, peer stores only) overrides it.
+    partial tiles travel by peer stores (`exchange = "peer-stores"`).  The choice is made PER CALL.  Measured on 4 and
+    8 B200s (profiles/r2_k8_trace_w4*.jsonl, _w8*.jsonl) neither exchange is bandwidth-bound at these sizes -- both
+    are chains of flag round trips -- and the in-switch chain (flag -> multimem.ld_reduce -> multimem.st -> flag) is
+    the longer one for large reductions (TP8, 10 MiB: 69-71 vs 60 us; TP4: 72 vs 53-57 us) but the shorter one for
+    small reductions at 8 ranks (TP8, 2.6 MiB: 32-35 vs 37-38 us).  Default: peer stores, except in-switch below
+    BSGL_K8_NVLS_MAX_BYTES (default 4 MiB) at world >= 8.  `BSGL_K8_EXCHANGE` = `nvls` (always in-switch), `peer` (IPC
+    buffers, peer stores only) or `symm-peer` (symmetric memory, peer stores only) overrides it.
 
     Every rank must make the same sequence of calls, which the replicated scheduler guarantees; the call counter
     lives in device memory, so the call can sit inside a captured CUDA graph.  The returned tensor is a view of
@@ -191,11 +191,11 @@ class FusedOProjAllReduce:
         if mode == "symm-peer":
             mc = 0
         self._nvls_always = mode == "nvls"
-        self._nvls_small = mode == "nvls-small"
+        self._nvls_small = mode in ("", "auto", "nvls-small")
         self._nvls_max_bytes = int(os.environ.get("BSGL_K8_NVLS_MAX_BYTES", str(4 << 20)))
         self.exchange = ("peer-stores (two-shot over NVLink peer memory)" +
-                         ("; nvls (multimem.ld_reduce / multimem.st over the NVSwitch multicast mapping) on request"
-                          if mc else "")) if world_size > 1 else "local (world 1)"
+                         ("; nvls (multimem.ld_reduce / multimem.st over the NVSwitch multicast mapping) for small "
+                          "reductions at 8 ranks or on request" if mc else "")) if world_size > 1 else "local (world 1)"
         self.last_exchange = None
         self._staging = base
         self._out = [p + self._off_out for p in base]
