@@ -114,6 +114,15 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap
       "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+// CTA-pair form: the bytes complete on the LEADER's barrier (the barrier at the same offset in the even CTA of the
+// pair: bit 24 of the shared-window address selects the CTA), whichever CTA of the pair issues the load.
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst_smem, const CUtensorMap* tmap, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          dst_smem),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+      : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
 }
@@ -211,7 +220,12 @@ __device__ __forceinline__ void reduce_owned_tile_nvls(const OprojComm& comm, in
   }
 }
 
-template <typename T>
+// PAIR: two CTAs of a (2,1,1) cluster compute one 256 x 256 output block with tcgen05.mma.cta_group::2 (M 256,
+// N 256): each CTA loads its own 128 rows of A and HALF of the weight tile (128 of the 256 rows) per k-block -- half
+// the operand bytes through L2 per flop of the 128 x 128 single-CTA tiles, and the per-instruction cost of the MMA
+// (43 clk + N / 2) is amortised over N = 256.  Each CTA still owns plain 128 x 128 output tiles (two per
+// block, side by side), so the exchange protocol is unchanged.
+template <typename T, bool PAIR>
 __global__ void __launch_bounds__(kOpThreads, 1)
 oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                        const __grid_constant__ OprojComm comm, int M, int N, int K, int rank, int world, int max_slots,
@@ -234,23 +248,41 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
     trace[1] = trace[2] = 0;
   }
 
+  // PAIR work unit q = (row pair qm, column pair qn): CTA `crank` of the pair owns rows of tile row 2 qm + crank and
+  // the two tile columns 2 qn, 2 qn + 1.
+  const uint32_t crank = PAIR ? tc::cluster_ctarank() : 0u;
+  const int n_qn = n_nt / 2, n_q = ((n_mt + 1) / 2) * n_qn;
+  const int unit0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int unit_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int n_units = PAIR ? n_q : n_tiles;
+  constexpr int kAccCols = PAIR ? 2 * kOpBN : kOpBN;                 // TMEM columns of one accumulator buffer
+
   const uint32_t bar0 = base + kOpStages * kOpStageBytes;
   const uint32_t full0 = bar0, empty0 = bar0 + 8 * kOpStages, accf0 = empty0 + 8 * kOpStages, acce0 = accf0 + 16;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kOpStages * kOpStageBytes + 8 * (2 * kOpStages + 4));
+  const uint32_t peerf0 = acce0 + 16;                                // leader: the peer CTA's stage has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kOpStages * kOpStageBytes + 8 * (3 * kOpStages + 4));
   if (threadIdx.x == 0) {
     for (int s = 0; s < kOpStages; ++s) {
       mbar_init(full0 + 8 * s, 1);      // producer's arrive.expect_tx; TMA completes the bytes
-      mbar_init(empty0 + 8 * s, 1);     // tcgen05.commit
+      mbar_init(empty0 + 8 * s, 1);     // tcgen05.commit (multicast to both CTAs of a pair)
+      mbar_init(peerf0 + 8 * s, 1);     // PAIR: remote arrive by the peer's relay warp
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(accf0 + 8 * b, 1);      // tcgen05.commit after a tile's last MMA
-      mbar_init(acce0 + 8 * b, 128);    // the epilogue threads, once the accumulator is in registers
+      // the epilogue threads, once the accumulator is in registers (PAIR: one arrive per epilogue warp of BOTH CTAs)
+      mbar_init(acce0 + 8 * b, PAIR ? 8 : 128);
     }
     fence_mbar_init();
   }
+  if constexpr (PAIR) tc::cluster_sync();                            // the peer's barriers exist before anyone signals them
   if (warp == 1) {
-    tc::tmem_alloc(smem_u32(tmem_slot), 256);
-    tc::tmem_relinquish();
+    if constexpr (PAIR) {
+      tc::tmem_alloc2(smem_u32(tmem_slot), 512);
+      tc::tmem_relinquish2();
+    } else {
+      tc::tmem_alloc(smem_u32(tmem_slot), 256);
+      tc::tmem_relinquish();
+    }
   }
   tc::fence_before_sync();
   __syncthreads();
@@ -263,41 +295,69 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
       tma_prefetch_desc(&tm_a);
       tma_prefetch_desc(&tm_b);
       uint32_t it = 0;
-      for (int i = blockIdx.x; i < n_tiles; i += gridDim.x) {
-        const int tile = (nvls || !grouped_order) ? i : tile_at(i, n_tiles, rank, world);
-        const int m0 = (tile / n_nt) * kOpBM, n0 = (tile % n_nt) * kOpBN;
+      for (int i = unit0; i < n_units; i += unit_step) {
+        int m0, n0;
+        if constexpr (PAIR) {
+          m0 = (2 * (i / n_qn) + (int)crank) * kOpBM;             // this CTA's 128 rows of the 256-row block
+          n0 = (2 * (i % n_qn)) * kOpBN + (int)crank * kOpBN;     // this CTA's half of the 256 weight rows
+        } else {
+          const int tile = (nvls || !grouped_order) ? i : tile_at(i, n_tiles, rank, world);
+          m0 = (tile / n_nt) * kOpBM;
+          n0 = (tile % n_nt) * kOpBN;
+        }
         for (int kb = 0; kb < n_kb; ++kb, ++it) {
           const uint32_t s = it % kOpStages, ph = (it / kOpStages) & 1u;
           mbar_wait_guarded(empty0 + 8 * s, ph ^ 1u);
-          mbar_arrive_expect_tx(full0 + 8 * s, kOpStageBytes);
           const uint32_t a_dst = base + s * kOpStageBytes;
-          tma_load_2d(a_dst, &tm_a, kb * kOpBK, m0, full0 + 8 * s);                      // rows past M arrive as zeros
-          tma_load_2d(a_dst + kOpBM * kOpBK * 2, &tm_b, kb * kOpBK, n0, full0 + 8 * s);
+          if constexpr (PAIR) {
+            // both CTAs' bytes complete on the leader's barrier, which expects the two stages together
+            if (crank == 0) mbar_arrive_expect_tx(full0 + 8 * s, 2 * kOpStageBytes);
+            tma_load_2d_pair(a_dst, &tm_a, kb * kOpBK, m0, full0 + 8 * s);               // rows past M arrive as zeros
+            tma_load_2d_pair(a_dst + kOpBM * kOpBK * 2, &tm_b, kb * kOpBK, n0, full0 + 8 * s);
+          } else {
+            mbar_arrive_expect_tx(full0 + 8 * s, kOpStageBytes);
+            tma_load_2d(a_dst, &tm_a, kb * kOpBK, m0, full0 + 8 * s);                    // rows past M arrive as zeros
+            tma_load_2d(a_dst + kOpBM * kOpBK * 2, &tm_b, kb * kOpBK, n0, full0 + 8 * s);
+          }
         }
       }
     }
   } else if (warp == 1) {
     // ======================================================== MMA issuer (warp-uniform loop, one elected lane)
-    constexpr uint32_t idesc = tc::instr_desc<T>(kOpBM, kOpBN, 0, 0);
+    constexpr uint32_t idesc = PAIR ? tc::instr_desc<T>(2 * kOpBM, 2 * kOpBN, 0, 0) : tc::instr_desc<T>(kOpBM, kOpBN, 0, 0);
     uint32_t it = 0, tcount = 0;
-    for (int i = blockIdx.x; i < n_tiles; i += gridDim.x, ++tcount) {
-      const uint32_t buf = tcount & 1u;
-      mbar_wait_guarded(acce0 + 8 * buf, ((tcount >> 1) & 1u) ^ 1u);
-      tc::fence_after_sync();
-      for (int kb = 0; kb < n_kb; ++kb, ++it) {
-        const uint32_t s = it % kOpStages, ph = (it / kOpStages) & 1u;
-        mbar_wait_guarded(full0 + 8 * s, ph);
+    if (PAIR && crank != 0) {
+      // the peer CTA of a pair issues nothing: the leader's MMAs read both CTAs' shared memory and write both TMEMs
+    } else {
+      for (int i = unit0; i < n_units; i += unit_step, ++tcount) {
+        const uint32_t buf = tcount & 1u;
+        mbar_wait_guarded(acce0 + 8 * buf, ((tcount >> 1) & 1u) ^ 1u);
         tc::fence_after_sync();
-        const uint32_t a = base + s * kOpStageBytes, b = a + kOpBM * kOpBK * 2;
-        if (tc::elect_one()) {
+        for (int kb = 0; kb < n_kb; ++kb, ++it) {
+          const uint32_t s = it % kOpStages, ph = (it / kOpStages) & 1u;
+          mbar_wait_guarded(full0 + 8 * s, ph);
+          tc::fence_after_sync();
+          const uint32_t a = base + s * kOpStageBytes, b = a + kOpBM * kOpBK * 2;
+          if (tc::elect_one()) {
 #pragma unroll
-          for (int kk = 0; kk < kOpBK / 16; ++kk)
-            tc::mma_ss(tmem + buf * kOpBN, tc::smem_desc_sw128(a + kk * 32, 16, 1024),
-                       tc::smem_desc_sw128(b + kk * 32, 16, 1024), idesc, (kb | kk) != 0 ? 1u : 0u);
-          tc::commit(empty0 + 8 * s);
-          if (kb == n_kb - 1) tc::commit(accf0 + 8 * buf);
+            for (int kk = 0; kk < kOpBK / 16; ++kk) {
+              if constexpr (PAIR)
+                tc::mma_ss2(tmem + buf * kAccCols, tc::smem_desc_sw128(a + kk * 32, 16, 1024),
+                            tc::smem_desc_sw128(b + kk * 32, 16, 1024), idesc, (kb | kk) != 0 ? 1u : 0u);
+              else
+                tc::mma_ss(tmem + buf * kAccCols, tc::smem_desc_sw128(a + kk * 32, 16, 1024),
+                           tc::smem_desc_sw128(b + kk * 32, 16, 1024), idesc, (kb | kk) != 0 ? 1u : 0u);
+            }
+            if constexpr (PAIR) {
+              tc::commit2(empty0 + 8 * s, 0b11);                       // both CTAs' stages are free again
+              if (kb == n_kb - 1) tc::commit2(accf0 + 8 * buf, 0b11);  // both CTAs' accumulators are complete
+            } else {
+              tc::commit(empty0 + 8 * s);
+              if (kb == n_kb - 1) tc::commit(accf0 + 8 * buf);
+            }
+          }
+          __syncwarp();
         }
-        __syncwarp();
       }
     }
   } else if (warp < 6) {
@@ -307,36 +367,57 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
     const int etid = (warp - 2) * 32 + lane;                  // 0..127
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     uint32_t tcount = 0;
-    for (int i = blockIdx.x; i < n_tiles; i += gridDim.x, ++tcount) {
-      const int tile = (nvls || !grouped_order) ? i : tile_at(i, n_tiles, rank, world);
-      const int owner = tile % world, slot = tile / world;
+    const uint32_t leader_acce0 = PAIR ? tc::mapa(acce0, 0) : 0u;
+    constexpr int kHalves = PAIR ? 2 : 1;                      // 128 x 128 output tiles per accumulator buffer
+    for (int i = unit0; i < n_units; i += unit_step, ++tcount) {
       const uint32_t buf = tcount & 1u;
       mbar_wait_guarded(accf0 + 8 * buf, (tcount >> 1) & 1u);
       tc::fence_after_sync();
-      uint32_t acc[4][32];
+#pragma unroll 1
+      for (int half = 0; half < kHalves; ++half) {
+        int tile;
+        bool valid = true;
+        if constexpr (PAIR) {
+          const int mt = 2 * (i / n_qn) + (int)crank;
+          tile = mt * n_nt + 2 * (i % n_qn) + half;
+          valid = mt < n_mt;                                   // odd number of tile rows: the peer's last rows do not exist
+        } else {
+          tile = (nvls || !grouped_order) ? i : tile_at(i, n_tiles, rank, world);
+        }
+        const int owner = tile % world, slot = tile / world;
+        uint32_t acc[4][32];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) tc::ld32(tmem + lane_base + buf * kOpBN + c * 32, acc[c]);
-      tc::wait_ld();
-      tc::fence_before_sync();
-      mbar_arrive(acce0 + 8 * buf);                           // the MMA warp may start the tile after next
-      // staging layout: 16-byte chunk c of row r at (c * 128 + r) * 16 -> a warp store is one 512-byte burst
-      // NVLS: the partial stays in this rank's own staging (the owner's multimem.ld_reduce pulls it through the
-      // switch); peer-store path: straight into the owner's staging over NVLink
-      uint4* dst = reinterpret_cast<uint4*>(
-          nvls ? comm.staging[rank] + (int64_t)tile * kOpTileBytes
-               : comm.staging[owner] + ((int64_t)rank * max_slots + slot) * kOpTileBytes);
+        for (int c = 0; c < 4; ++c) tc::ld32(tmem + lane_base + buf * kAccCols + half * kOpBN + c * 32, acc[c]);
+        tc::wait_ld();
+        if (half == kHalves - 1) {                             // the MMA warp may start the unit after next
+          tc::fence_before_sync();
+          if constexpr (PAIR) {
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive_cluster(leader_acce0 + 8 * buf);
+          } else {
+            mbar_arrive(acce0 + 8 * buf);
+          }
+        }
+        if (!valid) continue;
+        // staging layout: 16-byte chunk c of row r at (c * 128 + r) * 16 -> a warp store is one 512-byte burst
+        // NVLS: the partial stays in this rank's own staging (the owner's multimem.ld_reduce pulls it through the
+        // switch); peer-store path: straight into the owner's staging over NVLink
+        uint4* dst = reinterpret_cast<uint4*>(
+            nvls ? comm.staging[rank] + (int64_t)tile * kOpTileBytes
+                 : comm.staging[owner] + ((int64_t)rank * max_slots + slot) * kOpTileBytes);
 #pragma unroll
-      for (int c = 0; c < 16; ++c) {
-        const uint32_t* v = &acc[c >> 2][(c & 3) * 8];
-        uint4 pk;
-        pk.x = pack2<T>(__uint_as_float(v[0]), __uint_as_float(v[1]));
-        pk.y = pack2<T>(__uint_as_float(v[2]), __uint_as_float(v[3]));
-        pk.z = pack2<T>(__uint_as_float(v[4]), __uint_as_float(v[5]));
-        pk.w = pack2<T>(__uint_as_float(v[6]), __uint_as_float(v[7]));
-        dst[c * 128 + row] = pk;
+        for (int c = 0; c < 16; ++c) {
+          const uint32_t* v = &acc[c >> 2][(c & 3) * 8];
+          uint4 pk;
+          pk.x = pack2<T>(__uint_as_float(v[0]), __uint_as_float(v[1]));
+          pk.y = pack2<T>(__uint_as_float(v[2]), __uint_as_float(v[3]));
+          pk.z = pack2<T>(__uint_as_float(v[4]), __uint_as_float(v[5]));
+          pk.w = pack2<T>(__uint_as_float(v[6]), __uint_as_float(v[7]));
+          dst[c * 128 + row] = pk;
+        }
+        named_bar_sync(1, 128);    // bar.sync orders the 128 threads' stores before thread 0's release (cumulative)
+        if (etid == 0) st_release_sys(comm.flags[owner] + slot * kOpMaxWorld + rank, epoch);
       }
-      named_bar_sync(1, 128);      // bar.sync orders the 128 threads' stores before thread 0's release (cumulative)
-      if (etid == 0) st_release_sys(comm.flags[owner] + slot * kOpMaxWorld + rank, epoch);
     }
     if (etid == 0) trace[1] = globaltimer_ns();
 
@@ -377,10 +458,15 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
 
   }
 
+  tc::fence_before_sync();
   __syncthreads();
+  if constexpr (PAIR) tc::cluster_sync();   // the peer no longer signals this CTA's barriers nor reads its shared memory
   if (warp == 1) {
     tc::fence_after_sync();
-    tc::tmem_dealloc(tmem, 256);
+    if constexpr (PAIR)
+      tc::tmem_dealloc2(tmem, 512);
+    else
+      tc::tmem_dealloc(tmem, 256);
   }
   // the last CTA to get here closes the call: every CTA has read `epoch` by now, none will read it again
   if (threadIdx.x == 0) {
@@ -462,22 +548,42 @@ static int make_map(CUtensorMap* m, const void* ptr, int64_t rows, int64_t K, in
   return BSGL_OK;
 }
 
-template <typename T>
-static int launch_oproj(const CUtensorMap& ta, const CUtensorMap& tb, const OprojComm& comm, int M, int N, int K,
-                        int rank, int world, int max_slots, int max_tiles, uint64_t timeout_ns, cudaStream_t stream) {
-  auto kern = oproj_allreduce_kernel<T>;
+template <typename T, bool PAIR>
+static int launch_oproj_as(const CUtensorMap& ta, const CUtensorMap& tb, const OprojComm& comm, int M, int N, int K,
+                           int rank, int world, int max_slots, int max_tiles, uint64_t timeout_ns, int grid, int grouped,
+                           cudaStream_t stream) {
+  auto kern = oproj_allreduce_kernel<T, PAIR>;
   static thread_local int configured_dev = -1;
-  int dev = 0, sms = 0;
+  int dev = 0;
   BSGL_CUDA_TRY(cudaGetDevice(&dev));
   if (configured_dev != dev) {
     BSGL_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kOpSmemBytes));
     configured_dev = dev;
   }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kOpThreads);
+  cfg.dynamicSmemBytes = kOpSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = PAIR ? 2 : 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  BSGL_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, ta, tb, comm, M, N, K, rank, world, max_slots, max_tiles, timeout_ns,
+                                   grouped));
+  return check_launch("oproj_allreduce_kernel");
+}
+
+template <typename T>
+static int launch_oproj(const CUtensorMap& ta, const CUtensorMap& tb, const OprojComm& comm, int M, int N, int K,
+                        int rank, int world, int max_slots, int max_tiles, uint64_t timeout_ns, cudaStream_t stream) {
+  int dev = 0, sms = 0;
+  BSGL_CUDA_TRY(cudaGetDevice(&dev));
   BSGL_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int n_tiles = ((M + kOpBM - 1) / kOpBM) * (N / kOpBN);
-  // every CTA must be resident: phase 2 waits on tiles other CTAs of this grid produce (one CTA per SM: 197 KB of
-  // shared memory each; a persistent kernel of another stream holding SMs would stall it until the timeout)
-  const int grid = n_tiles < sms ? n_tiles : sms;
+  const int n_mt = (M + kOpBM - 1) / kOpBM, n_nt = N / kOpBN, n_tiles = n_mt * n_nt;
   // Visiting order of the peer-store path.  "global" (default): every rank walks the tiles in the same order, so
   // the `world` partials of a tile reach its owner at about the same time and the owner's reduction trails the
   // GEMM tile by tile (the 148 tiles in flight cover all owners evenly: no hot link).  "grouped": owner by owner
@@ -486,9 +592,49 @@ static int launch_oproj(const CUtensorMap& ta, const CUtensorMap& tb, const Opro
     const char* e = getenv("BSGL_K8_TILE_ORDER");
     return (e && e[0] == 'g' && e[1] == 'r') ? 1 : 0;
   }();
-  kern<<<grid, kOpThreads, kOpSmemBytes, stream>>>(ta, tb, comm, M, N, K, rank, world, max_slots, max_tiles,
-                                                   timeout_ns, grouped);
-  return check_launch("oproj_allreduce_kernel");
+  // CTA pairs (cta_group::2, 256 x 256 blocks): measured 67.5 vs 82.0 us at world 1 on 1024 x 5120 x 5120 (795 vs
+  // 655 TFLOP/s), but 69.4 vs 62.0 us at TP2 on the same output: 80 blocks on 74 pairs finish in two coarse rounds, so
+  // all partial tiles are published in two bursts, where the 320 single-CTA tiles spread their peer stores under the
+  // GEMM.  Chosen automatically only without an exchange (world 1) and when the single-CTA tiles would need more
+  // than one wave (below that they spread over twice as many SMs).  BSGL_K8_GEMM=single|pair overrides.
+  const char* gm = getenv("BSGL_K8_GEMM");                    // read per call: tests and benches flip it in-process
+  const int gemm_mode = !gm ? 0 : (gm[0] == 's' ? 1 : (gm[0] == 'p' ? 2 : 0));
+  const bool pair_ok = n_mt >= 2 && n_nt % 2 == 0 && sms >= 2;
+  const bool pair = pair_ok && (gemm_mode == 2 || (gemm_mode == 0 && world == 1 && n_tiles > sms));
+  // every CTA must be resident: phase 2 waits on tiles other CTAs of this grid produce (one CTA per SM: 197 KB of
+  // shared memory each; a persistent kernel of another stream holding SMs would stall it until the timeout)
+  if (pair) {
+    // how many CTA pairs the device can hold at once (a pair needs both SMs of a TPC), asked once per device
+    static thread_local int pairs_dev = -1, pairs_max = 0;
+    if (pairs_dev != dev) {
+      auto kern = oproj_allreduce_kernel<T, true>;
+      BSGL_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kOpSmemBytes));
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)(2 * (sms / 2)));
+      cfg.blockDim = dim3(kOpThreads);
+      cfg.dynamicSmemBytes = kOpSmemBytes;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = 2;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      int n = 0;
+      BSGL_CUDA_TRY(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+      pairs_max = n;
+      pairs_dev = dev;
+    }
+    const int n_q = ((n_mt + 1) / 2) * (n_nt / 2);
+    const int cap = pairs_max < sms / 2 ? pairs_max : sms / 2;
+    BSGL_REQUIRE(cap >= 1, "bsgl_oproj_allreduce: the device cannot hold one CTA pair of this kernel");
+    const int pairs = n_q < cap ? n_q : cap;
+    return launch_oproj_as<T, true>(ta, tb, comm, M, N, K, rank, world, max_slots, max_tiles, timeout_ns, 2 * pairs,
+                                    grouped, stream);
+  }
+  const int grid = n_tiles < sms ? n_tiles : sms;
+  return launch_oproj_as<T, false>(ta, tb, comm, M, N, K, rank, world, max_slots, max_tiles, timeout_ns, grid, grouped,
+                                   stream);
 }
 
 }  // namespace bsgl

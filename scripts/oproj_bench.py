@@ -73,11 +73,17 @@ def main():
             return [round(float(x), 1) for x in t]
 
         line = {"T": T, "hidden": hidden, "K_per_rank": K, "world": world}
+        flops = 2.0 * T * hidden * K
+        for mode in ("single", "pair"):                    # K8's GEMM form: 128 x 128 single-CTA tiles / 256 x 256 CTA pairs
+            os.environ["BSGL_K8_GEMM"] = mode
+            d, h = timed(fused)
+            line[f"fused_{mode}_device_us"], line[f"fused_{mode}_tflops_per_rank"] = d, round(flops / (d * 1e-6) / 1e12, 1)
+        os.environ.pop("BSGL_K8_GEMM", None)
         for name, fn in (("fused", fused), ("nccl_pair", pair), ("gemm_only", gemm)):
             d, h = timed(fn)
             line[name + "_device_us"], line[name + "_host_us"] = d, h
-        flops = 2.0 * T * hidden * K
         line["fused_tflops_per_rank"] = round(flops / (line["fused_device_us"] * 1e-6) / 1e12, 1)
+        line["gemm_only_tflops"] = round(flops / (line["gemm_only_device_us"] * 1e-6) / 1e12, 1)
         if rank == 0:
             print(json.dumps(line), flush=True)
         comm.close()

@@ -24,9 +24,17 @@ def _tp():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("gemm", ["auto", "single", "pair"])
 @pytest.mark.parametrize("T,hidden,K,dtype", [(1024, 5120, 640, torch.bfloat16), (333, 1536, 768, torch.bfloat16),
-                                              (1, 3584, 3584, torch.bfloat16), (130, 256, 64, torch.float16)])
-def test_fused_oproj_world1_matches_fp32_matmul(T, hidden, K, dtype):
+                                              (1, 3584, 3584, torch.bfloat16), (130, 256, 64, torch.float16),
+                                              (1000, 5120, 2560, torch.bfloat16)])
+def test_fused_oproj_world1_matches_fp32_matmul(T, hidden, K, dtype, gemm, monkeypatch):
+    """`gemm`: the single-CTA 128 x 128 tiles, the cta_group::2 256 x 256 pair blocks (forced: also odd numbers of tile
+    rows, where the peer CTA of the last row pair has no rows), or the library's own choice."""
+    if gemm != "auto":
+        monkeypatch.setenv("BSGL_K8_GEMM", gemm)
+    else:
+        monkeypatch.delenv("BSGL_K8_GEMM", raising=False)
     tp = _tp()
     comm = tp.FusedOProjAllReduce(0, 1, None, hidden=hidden, max_tokens=1024, dtype=dtype)
     try:
