@@ -373,35 +373,32 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
       const uint32_t buf = tcount & 1u;
       mbar_wait_guarded(accf0 + 8 * buf, (tcount >> 1) & 1u);
       tc::fence_after_sync();
-#pragma unroll 1
-      for (int half = 0; half < kHalves; ++half) {
-        int tile;
-        bool valid = true;
-        if constexpr (PAIR) {
-          const int mt = 2 * (i / n_qn) + (int)crank;
-          tile = mt * n_nt + 2 * (i % n_qn) + half;
-          valid = mt < n_mt;                                   // odd number of tile rows: the peer's last rows do not exist
-        } else {
-          tile = (nvls || !grouped_order) ? i : tile_at(i, n_tiles, rank, world);
-        }
-        const int owner = tile % world, slot = tile / world;
-        uint32_t acc[4][32];
+      uint32_t acc[4][32];
+      auto tile_of = [&](int half) {
+        if constexpr (PAIR) return (2 * (i / n_qn) + (int)crank) * n_nt + 2 * (i % n_qn) + half;
+        return (nvls || !grouped_order) ? i : tile_at(i, n_tiles, rank, world);
+      };
+      // odd number of tile rows: the peer CTA's rows of the last row pair do not exist
+      const bool valid = !PAIR || (2 * (i / n_qn) + (int)crank) < n_mt;
+      auto load_half = [&](int half) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) tc::ld32(tmem + lane_base + buf * kAccCols + half * kOpBN + c * 32, acc[c]);
         tc::wait_ld();
-        if (half == kHalves - 1) {                             // the MMA warp may start the unit after next
-          tc::fence_before_sync();
-          if constexpr (PAIR) {
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive_cluster(leader_acce0 + 8 * buf);
-          } else {
-            mbar_arrive(acce0 + 8 * buf);
-          }
+      };
+      auto release_acc = [&]() {                               // the MMA warp may start the unit after next
+        tc::fence_before_sync();
+        if constexpr (PAIR) {
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive_cluster(leader_acce0 + 8 * buf);
+        } else {
+          mbar_arrive(acce0 + 8 * buf);
         }
-        if (!valid) continue;
-        // staging layout: 16-byte chunk c of row r at (c * 128 + r) * 16 -> a warp store is one 512-byte burst
-        // NVLS: the partial stays in this rank's own staging (the owner's multimem.ld_reduce pulls it through the
-        // switch); peer-store path: straight into the owner's staging over NVLink
+      };
+      // staging layout: 16-byte chunk c of row r at (c * 128 + r) * 16 -> a warp store is one 512-byte burst
+      // NVLS: the partial stays in this rank's own staging (the owner's multimem.ld_reduce pulls it through the
+      // switch); peer-store path: straight into the owner's staging over NVLink
+      auto store_tile = [&](int tile) {
+        const int owner = tile % world, slot = tile / world;
         uint4* dst = reinterpret_cast<uint4*>(
             nvls ? comm.staging[rank] + (int64_t)tile * kOpTileBytes
                  : comm.staging[owner] + ((int64_t)rank * max_slots + slot) * kOpTileBytes);
@@ -415,8 +412,27 @@ oproj_allreduce_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
           pk.w = pack2<T>(__uint_as_float(v[6]), __uint_as_float(v[7]));
           dst[c * 128 + row] = pk;
         }
+      };
+      auto publish_tile = [&](int tile) {
         named_bar_sync(1, 128);    // bar.sync orders the 128 threads' stores before thread 0's release (cumulative)
-        if (etid == 0) st_release_sys(comm.flags[owner] + slot * kOpMaxWorld + rank, epoch);
+        if (etid == 0) st_release_sys(comm.flags[tile % world] + (tile / world) * kOpMaxWorld + rank, epoch);
+      };
+      load_half(0);
+      if constexpr (PAIR) {
+        // the accumulator is handed back before the first tile's (slow, system-scope) release: the leader's next
+        // block waits for BOTH CTAs' epilogues
+        if (valid) store_tile(tile_of(0));
+        load_half(1);
+        release_acc();
+        if (valid) {
+          publish_tile(tile_of(0));
+          store_tile(tile_of(1));
+          publish_tile(tile_of(1));
+        }
+      } else {
+        release_acc();
+        store_tile(tile_of(0));
+        publish_tile(tile_of(0));
       }
     }
     if (etid == 0) trace[1] = globaltimer_ns();
