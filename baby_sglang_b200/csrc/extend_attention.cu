@@ -4,6 +4,11 @@
 // (:54-57), K/V gather of prefix + new tokens (:58-59), GQA repeat_interleave (:61-66), dense
 // additive mask `col > prefix + row` (:74-92), SDPA (:94-101), cat (:110).
 //
+// PERSISTENT: one CTA per SM walks the work items (dispatch order, dealt boustrophedon over the CTAs); TMEM, the
+// mbarriers (phases carried across items) and the K/V ring live for the whole launch, and the producers gather the
+// next item's first K/V tiles and its Q tiles while the current item drains -- the ~9 us of launch + allocation +
+// pipeline fill a one-item CTA paid are gone (prefix 1024: +8 %, no prefix: +17 %; long prefixes, which run at the
+// board's power cap, +-1 %).
 // Work item = (request, KV head, q chunk).  The G q heads that share a KV head are packed into the
 // M dimension: packed row m = token * G + head, 256 packed rows per chunk = two 128-row tiles
 // (A and B) that share one stream of K/V tiles, so every gathered KV row feeds 2 x 128 MMA rows.
@@ -71,7 +76,8 @@ struct ExtCfg {
   static constexpr int Q_OFF = 0;
   static constexpr int RING_OFF = 2 * TILE_BYTES;
   static constexpr int BAR_OFF = RING_OFF + RING * TILE_BYTES;
-  static constexpr int N_BARS = 1 + 2 * RING + 2 + 2 * kExtPParts;   // q_full, full/empty per slot, s_full[2], p_full[parts][2]
+  // q_full, q_free, full/empty per slot, s_full[2], p_full[parts][2], o_full[2]
+  static constexpr int N_BARS = 2 + 2 * RING + 2 + 2 * kExtPParts + 2;
   static constexpr int MISC_OFF = BAR_OFF + N_BARS * 8;
   static constexpr int SMEM_BYTES = MISC_OFF + 64;
   static_assert(SMEM_BYTES <= 227 * 1024, "extend kernel shared memory over budget");
@@ -82,17 +88,13 @@ struct ExtCfg {
   static constexpr int NR = (128 + RSTEP - 1) / RSTEP;   // rows per producer thread per 128-row tile
 };
 
-struct ExtItem {
-  int req, chunk, found, pad;
-};
-
 template <typename T, int D, int EXPMODE>
 __global__ void __launch_bounds__(kExtThreads, 1)
 extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, const T* __restrict__ v_slab,
                         const int32_t* __restrict__ req_to_token, int64_t pt_stride,
                         const int64_t* __restrict__ req_pool_indices, const int64_t* __restrict__ prefix_lens,
                         const int32_t* __restrict__ qo_indptr, const int32_t* __restrict__ req_order, int batch,
-                        int n_q_heads, int n_kv_heads, float scale_log2, T* __restrict__ out) {
+                        int n_q_heads, int n_kv_heads, float scale_log2, T* __restrict__ out, int total_vb) {
   using C = ExtCfg<D>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];   // SWIZZLE_128B operand tiles need 1024-byte alignment
   const uint32_t smem_base = smem_u32(smem_raw);
@@ -102,15 +104,31 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
   BSGL_TR_INIT();
   const int G = n_q_heads / n_kv_heads;
   const int TQ = kExtRows / G;                // tokens per chunk
-  const int h = blockIdx.x % n_kv_heads;      // KV head: fastest, so the heads of one chunk run together
 
-  // ---- which (request, chunk) is this CTA?  chunk counts are ceil(ext_i / TQ); warp 0 scans them in
-  // dispatch order (req_order: longest KV first, so the last wave is made of the cheapest requests).
-  ExtItem* item = reinterpret_cast<ExtItem*>(smem + C::MISC_OFF + 16);
-  if (warp == 0) {
-    const int target = blockIdx.x / n_kv_heads;
-    int base = 0, found = 0;
-    for (int i0 = 0; i0 < batch && !found; i0 += 32) {
+  // ---- PERSISTENT: one CTA per SM walks the work items vb = blockIdx.x, blockIdx.x + gridDim.x, ...  (vb % Hkv =
+  // KV head, fastest, so the heads of one chunk run together; vb / Hkv = position in dispatch order).  Every warp
+  // resolves an item by itself (warp scan over the chunk counts ceil(ext_i / TQ) in dispatch order -- req_order:
+  // longest KV first, and a request's longest-KV chunk first), so the roles stay decoupled: barrier phases, the
+  // K/V ring and TMEM carry across items, the producers prefetch the next item's tiles while this one drains,
+  // and nothing is re-allocated or re-initialised per item.
+  struct Work {
+    int found, req, h, q_begin, prefix, t0, n_tok, kv_end, nkv;
+  };
+  // Items come in decreasing cost (dispatch order), so the rounds are dealt boustrophedon: CTA b takes position b of
+  // the even rounds and position G - 1 - b of the odd ones, which evens out the per-CTA totals without a shared counter
+  // (plain round-robin gave CTA 0 the dearest item of every round: 7 % slower than the hardware's greedy block
+  // scheduler on the ragged C3 mix).
+  auto vb_of = [&](int round) {
+    const int g = (int)gridDim.x, b = (int)blockIdx.x;
+    return round * g + ((round & 1) ? g - 1 - b : b);
+  };
+  auto find_work = [&](int vb) {
+    Work w;
+    w.found = 0;
+    w.h = vb % n_kv_heads;
+    const int target = vb / n_kv_heads;
+    int base = 0, req = 0, chunk = 0;
+    for (int i0 = 0; i0 < batch && !w.found; i0 += 32) {
       const int pos = i0 + lane;
       const int i = pos < batch ? (req_order ? req_order[pos] : pos) : 0;
       const int cnt = pos < batch ? (qo_indptr[i + 1] - qo_indptr[i] + TQ - 1) / TQ : 0;
@@ -122,34 +140,43 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
       }
       const int lo = base + incl - cnt;
       const bool hit = target >= lo && target < lo + cnt;
-      if (hit) {
-        item->req = i;
-        item->chunk = cnt - 1 - (target - lo);   // a request's longest-KV chunk is dispatched first
+      const uint32_t ballot = __ballot_sync(0xffffffffu, hit);
+      if (ballot) {
+        const int src = __ffs(ballot) - 1;
+        req = __shfl_sync(0xffffffffu, i, src);
+        chunk = __shfl_sync(0xffffffffu, cnt - 1 - (target - lo), src);   // a request's longest-KV chunk goes first
+        w.found = 1;
       }
-      found = __any_sync(0xffffffffu, hit);
       base += __shfl_sync(0xffffffffu, incl, 31);
     }
-    if (lane == 0) item->found = found;
-  }
-  __syncthreads();
-  if (!item->found) return;
-  const int req = item->req;
-  const int q_begin = qo_indptr[req];
-  const int ext = qo_indptr[req + 1] - q_begin;
-  const int prefix = (int)prefix_lens[req];
-  const int t0 = item->chunk * TQ;                       // first token of the chunk inside the extend
-  const int n_tok = min(TQ, ext - t0);
-  const int kv_end = prefix + t0 + n_tok;                // KV tokens the last row of the chunk sees
-  const int nkv = (kv_end + kExtKvTile - 1) / kExtKvTile;
+    if (w.found) {
+      w.req = req;
+      w.q_begin = qo_indptr[req];
+      const int ext = qo_indptr[req + 1] - w.q_begin;
+      w.prefix = (int)prefix_lens[req];
+      w.t0 = chunk * TQ;                                   // first token of the chunk inside the extend
+      w.n_tok = min(TQ, ext - w.t0);
+      w.kv_end = w.prefix + w.t0 + w.n_tok;                // KV tokens the last row of the chunk sees
+      w.nkv = (w.kv_end + kExtKvTile - 1) / kExtKvTile;
+    }
+    return w;
+  };
 
   // ---- barriers, TMEM
   const uint32_t bar0 = smem_base + C::BAR_OFF;
   constexpr int RING = C::RING;
   const uint32_t q_full = bar0;
   const uint32_t full0 = bar0 + 8, empty0 = full0 + 8 * RING, s_full = empty0 + 8 * RING, p_full = s_full + 16;
+  const uint32_t q_free = p_full + 16 * kExtPParts;     // the item's last S MMA has read the Q tiles
+  // O_X holds the item's last PV.  Its own barrier (one completion per item): on s_full it would be a second
+  // completion between two waits of the softmax warps, which a parity wait cannot tell from none.
+  const uint32_t o_full = q_free + 8;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::MISC_OFF);
   if (threadIdx.x == 0) {
     mbar_init(q_full, kExtProducerThreads);       // one cp.async-completion arrive per producer thread
+    mbar_init(q_free, 1);                         // tcgen05.commit
+    mbar_init(o_full, 1);                         // tcgen05.commit
+    mbar_init(o_full + 8, 1);
     for (int s = 0; s < RING; ++s) {
       mbar_init(full0 + 8 * s, kExtProducerThreads);
       mbar_init(empty0 + 8 * s, 1);               // tcgen05.commit
@@ -179,17 +206,23 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
     const int m = x * 128 + row;                           // packed row in the chunk
     const int tok = m / G;
     const int head = m - tok * G;
-    const bool valid = tok < n_tok && m < TQ * G;
-    // last visible KV column.  Padding rows (zero-filled Q, never stored) see everything: a row that
-    // masked every tile would drag its whole warp through the mask code on every tile.
-    const int limit = valid ? prefix + t0 + tok : 0x3fffffff;
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t s_addr = tmem + lane_base + x * 128;
     const uint32_t o_addr = tmem + lane_base + C::O_COL + x * D;
+    uint32_t sf_par = 0;                                   // parity of the s_full[x] completions consumed by earlier items
+   for (int round = 0;; ++round) {
+    const int vb = vb_of(round);
+    if (vb >= total_vb) break;
+    const Work W = find_work(vb);
+    if (!W.found) break;
+    const int nkv = W.nkv;
+    // last visible KV column.  Padding rows (zero-filled Q, never stored) see everything: a row that
+    // masked every tile would drag its whole warp through the mask code on every tile.
+    const int limit = (tok < W.n_tok && m < TQ * G) ? W.prefix + W.t0 + tok : 0x3fffffff;
     float m_used = -INFINITY, l = 0.f;
 
     for (int j = 0; j < nkv; ++j) {
-      mbar_wait_guarded(s_full + 8 * x, j & 1);
+      mbar_wait_guarded(s_full + 8 * x, (sf_par + j) & 1);
       tc::fence_after_sync();
       if (lane == 0) BSGL_TR(warp, j, 0);
       uint32_t s[4][32];
@@ -313,10 +346,17 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
       }
     }
     // ---- epilogue: O / l -> out[token, head, :]
-    mbar_wait_guarded(s_full + 8 * x, nkv & 1);
+    mbar_wait_guarded(o_full + 8 * x, round & 1);          // one item per round
+    sf_par ^= (uint32_t)nkv & 1u;
     tc::fence_after_sync();
+    // the item is resolved once more here, so that its address fields are not live registers across the KV loop
+    // (the softmax warpgroups run at their 208-register ceiling)
+    int vb_again = vb;
+    asm volatile("" : "+r"(vb_again));
+    const Work E = find_work(vb_again);
+    const bool valid = limit != 0x3fffffff;
     const float inv = (valid && l > 0.f) ? 1.f / l : 0.f;
-    T* orow = out + ((int64_t)(q_begin + t0 + tok) * n_q_heads + (int64_t)h * G + head) * D;
+    T* orow = out + ((int64_t)(E.q_begin + E.t0 + tok) * n_q_heads + (int64_t)E.h * G + head) * D;
 #pragma unroll
     for (int c = 0; c < D / 32; ++c) {
       uint32_t o[32];
@@ -334,7 +374,10 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
         }
       }
     }
+    // O_X is read: the next item's first PV_X (which overwrites it) is issued only after this thread has published
+    // that item's first P group, i.e. after this point in program order
     tc::fence_before_sync();
+   }   // next work item
   } else if (warp == kExtMmaWarp) {
     // ============================================================ MMA issuer
     // The whole warp runs the loop with uniform control flow (descriptors, addresses and counters
@@ -376,33 +419,53 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
                        tc::smem_desc_sw128(vb + kk * 2048, C::HALF_BYTES, 1024), idesc_pv, (acc || kk > 0) ? 1u : 0u);
           }
           if (hlf == kExtPParts - 1 && release_v) tc::commit(empty0 + 8 * slot);
-          if (hlf == kExtPParts - 1 && last) tc::commit(s_full + 8 * x);     // O_X complete
+          if (hlf == kExtPParts - 1 && last) tc::commit(o_full + 8 * x);     // O_X complete
         }
         __syncwarp();
       };
-      mbar_wait_guarded(q_full, 0);
-      wait_tile(0);
-      issue_s(0, 0, false);
-      issue_s(1, 0, true);
-      for (int j = 0; j < nkv; ++j) {
-        const int uv = 2 * j + 1, uk = 2 * j + 2;     // V_j, K_{j+1}
-        wait_tile(uv);
-        if (lane == 0) BSGL_TR(8, j, 0);
+      auto commit_q_free = [&]() {                     // the item's last S MMAs are issued: Q may be overwritten
+        if (tc::elect_one()) tc::commit(q_free);
+        __syncwarp();
+      };
+      uint32_t items_done = 0, u0 = 0, step0 = 0;      // items, ring tiles and softmax steps of earlier items
+      for (int round = 0;; ++round) {
+        const int vb = vb_of(round);
+        if (vb >= total_vb) break;
+        const Work W = find_work(vb);
+        if (!W.found) break;
+        const int nkv = W.nkv;
+        mbar_wait_guarded(q_full, items_done & 1);
+        wait_tile(u0);
+        // S_X(0) overwrites the previous item's last P_X: the tensor pipe runs in issue order, PV_X(last) is ahead
+        issue_s(0, u0, false);
+        issue_s(1, u0, true);
+        if (nkv == 1) commit_q_free();
+        for (int j = 0; j < nkv; ++j) {
+          const int uv = u0 + 2 * j + 1, uk = u0 + 2 * j + 2;     // V_j, K_{j+1}
+          wait_tile(uv);
+          if (lane == 0) BSGL_TR(8, j, 0);
 #pragma unroll
-        for (int x = 0; x < 2; ++x) {
+          for (int x = 0; x < 2; ++x) {
 #pragma unroll
-          for (int hlf = 0; hlf < kExtPParts; ++hlf) {
-            mbar_wait_guarded(p_full + 16 * hlf + 8 * x, j & 1);
-            tc::fence_after_sync();
-            if (lane == 0) BSGL_TR(8, j, 1 + 3 * x + hlf);
-            issue_pv(x, uv, hlf, j > 0, x == 1, j + 1 >= nkv);
-          }
-          if (j + 1 < nkv) {
-            if (x == 0) wait_tile(uk);
-            issue_s(x, uk, x == 1);
-            if (lane == 0) BSGL_TR(8, j, 3 + 3 * x);
+            for (int hlf = 0; hlf < kExtPParts; ++hlf) {
+              // (j = 0: the softmax threads of tile x publish this group only after their epilogue of the previous
+              // item has read O_X, which this PV overwrites)
+              mbar_wait_guarded(p_full + 16 * hlf + 8 * x, (step0 + j) & 1);
+              tc::fence_after_sync();
+              if (lane == 0) BSGL_TR(8, j, 1 + 3 * x + hlf);
+              issue_pv(x, uv, hlf, j > 0, x == 1, j + 1 >= nkv);
+            }
+            if (j + 1 < nkv) {
+              if (x == 0) wait_tile(uk);
+              issue_s(x, uk, x == 1);
+              if (x == 1 && j + 2 == nkv) commit_q_free();
+              if (lane == 0) BSGL_TR(8, j, 3 + 3 * x);
+            }
           }
         }
+        u0 += 2 * nkv;
+        step0 += nkv;
+        ++items_done;
       }
     }
   } else {
@@ -415,50 +478,66 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
     const int cc = c16 & 7;
     auto dst_of = [&](int r) { return col_off + (uint32_t)r * 128u + (uint32_t)((cc ^ (r & 7)) << 4); };
 
-    // Q: packed row m = token * G + head; the G heads of a token are contiguous in q.
-    for (int mrow = r0; mrow < kExtRows; mrow += C::RSTEP) {
-      const int tok = mrow / G;
-      const int head = mrow - tok * G;
-      const bool ok = tok < n_tok && mrow < TQ * G;
-      const T* src = q + ((int64_t)(q_begin + t0 + (ok ? tok : 0)) * n_q_heads + (int64_t)h * G + (ok ? head : 0)) * D +
-                     c16 * 8;
-      cp_async16_zfill(q_smem + (mrow >> 7) * C::TILE_BYTES + dst_of(mrow & 127), src, ok ? 16u : 0u);
-    }
-    cp_async_mbar_arrive(q_full);
-
-    const int32_t* idxp = req_to_token + req_pool_indices[req] * pt_stride;
     const int64_t slab_row = (int64_t)n_kv_heads * D;
-    const T* kb = k_slab + (int64_t)h * D + c16 * 8;
-    const T* vb = v_slab + (int64_t)h * D + c16 * 8;
-    for (int j = 0; j < nkv; ++j) {
-      // page-table entries of this tile (-1 = past the chunk's last visible token: zero-fill);
-      // their latency hides behind the wait for a free slot
-      int idx[C::NR];
-#pragma unroll
-      for (int i = 0; i < C::NR; ++i) {
-        const int r = r0 + i * C::RSTEP;
-        const int t = j * kExtKvTile + r;
-        idx[i] = (r < kExtKvTile && t < kv_end) ? __ldg(idxp + t) : -1;
-      }
-#pragma unroll
-      for (int kv = 0; kv < 2; ++kv) {               // K_j then V_j, same rows
-        const int u = 2 * j + kv;
-        const int slot = u % RING;
-        mbar_wait_guarded(empty0 + 8 * slot, ((u / RING) & 1) ^ 1);
-        if (p == 0) BSGL_TR(9, j, 2 * kv);
-        const T* base = kv == 0 ? kb : vb;
-        const uint32_t dst = ring_smem + slot * C::TILE_BYTES;
+    uint32_t items_done = 0, u0 = 0;                       // items and ring tiles of earlier items
+    for (int round = 0;; ++round) {
+      const int vb = vb_of(round);
+      if (vb >= total_vb) break;
+      const Work W = find_work(vb);
+      if (!W.found) break;
+      const int nkv = W.nkv, kv_end = W.kv_end;
+      const int32_t* idxp = req_to_token + req_pool_indices[W.req] * pt_stride;
+      const T* kb = k_slab + (int64_t)W.h * D + c16 * 8;
+      const T* vb_ = v_slab + (int64_t)W.h * D + c16 * 8;
+      // K_j then V_j (same rows) into the next two ring slots
+      auto load_pair = [&](int j) {
+        // page-table entries of this tile (-1 = past the chunk's last visible token: zero-fill);
+        // their latency hides behind the wait for a free slot
+        int idx[C::NR];
 #pragma unroll
         for (int i = 0; i < C::NR; ++i) {
           const int r = r0 + i * C::RSTEP;
-          if (r < kExtKvTile && !((EXPMODE == 5 || EXPMODE == 6) && u >= RING)) {   // 5/6: timing experiment, no gather
-            const bool ok = idx[i] >= 0;
-            cp_async16_zfill(dst + dst_of(r), base + (ok ? idx[i] : 0) * slab_row, ok ? 16u : 0u);
-          }
+          const int t = j * kExtKvTile + r;
+          idx[i] = (r < kExtKvTile && t < kv_end) ? __ldg(idxp + t) : -1;
         }
-        cp_async_mbar_arrive(full0 + 8 * slot);      // arrives when this thread's copies have landed
-        if (p == 0) BSGL_TR(9, j, 2 * kv + 1);
+#pragma unroll
+        for (int kv = 0; kv < 2; ++kv) {
+          const uint32_t u = u0 + 2 * j + kv;
+          const uint32_t slot = u % RING;
+          mbar_wait_guarded(empty0 + 8 * slot, ((u / RING) & 1) ^ 1);
+          if (p == 0) BSGL_TR(9, j, 2 * kv);
+          const T* base = kv == 0 ? kb : vb_;
+          const uint32_t dst = ring_smem + slot * C::TILE_BYTES;
+#pragma unroll
+          for (int i = 0; i < C::NR; ++i) {
+            const int r = r0 + i * C::RSTEP;
+            if (r < kExtKvTile && !((EXPMODE == 5 || EXPMODE == 6) && u >= RING)) {   // 5/6: timing experiment, no gather
+              const bool ok = idx[i] >= 0;
+              cp_async16_zfill(dst + dst_of(r), base + (ok ? idx[i] : 0) * slab_row, ok ? 16u : 0u);
+            }
+          }
+          cp_async_mbar_arrive(full0 + 8 * slot);    // arrives when this thread's copies have landed
+          if (p == 0) BSGL_TR(9, j, 2 * kv + 1);
+        }
+      };
+      // The item's first K/V tiles go into whatever ring slots the previous item has already released, BEFORE
+      // the wait for its last S MMA to let go of the Q tiles: the pipeline fill of this item hides behind the
+      // drain of the previous one.
+      load_pair(0);
+      if (items_done > 0) mbar_wait_guarded(q_free, (items_done - 1) & 1);
+      // Q: packed row m = token * G + head; the G heads of a token are contiguous in q.
+      for (int mrow = r0; mrow < kExtRows; mrow += C::RSTEP) {
+        const int tok = mrow / G;
+        const int head = mrow - tok * G;
+        const bool ok = tok < W.n_tok && mrow < TQ * G;
+        const T* src = q + ((int64_t)(W.q_begin + W.t0 + (ok ? tok : 0)) * n_q_heads + (int64_t)W.h * G + (ok ? head : 0)) * D +
+                       c16 * 8;
+        cp_async16_zfill(q_smem + (mrow >> 7) * C::TILE_BYTES + dst_of(mrow & 127), src, ok ? 16u : 0u);
       }
+      cp_async_mbar_arrive(q_full);
+      for (int j = 1; j < nkv; ++j) load_pair(j);
+      u0 += 2 * nkv;
+      ++items_done;
     }
     cp_async_wait_all();                             // nothing of this CTA is in flight at exit
   }
@@ -492,14 +571,24 @@ static int launch_extend(const void* q, const void* k_slab, const void* v_slab, 
   }
   const int G = n_q_heads / n_kv_heads;
   const int TQ = kExtRows / G;
-  // sum_i ceil(ext_i / TQ) <= floor(T / TQ) + batch; surplus CTAs exit before touching TMEM
+  // sum_i ceil(ext_i / TQ) <= floor(T / TQ) + batch work items per KV head; one persistent CTA per SM walks them
+  // (items past the real count resolve to "not found" and end a CTA's walk)
   const int64_t max_chunks = n_tokens / TQ + batch;
   BSGL_REQUIRE(max_chunks * n_kv_heads < (1ll << 31), "bsgl_extend_attention: too many q chunks");
-  dim3 grid((unsigned)(max_chunks * n_kv_heads));
+  const int total_vb = (int)(max_chunks * n_kv_heads);
+  static thread_local int sms_dev = -1, sms = 0;
+  if (sms_dev != dev) {
+    BSGL_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    sms_dev = dev;
+  }
+  // BSGL_EXT_PERSIST=0: one CTA per work item (the loop then ends after its first round) -- experiments only
+  const char* pe = getenv("BSGL_EXT_PERSIST");
+  const bool persist = !(pe && pe[0] == '0');
+  dim3 grid((unsigned)((total_vb < sms || !persist) ? total_vb : sms));
   const float scale_log2 = sm_scale * 1.4426950408889634f;
   kern<<<grid, kExtThreads, C::SMEM_BYTES, stream>>>((const T*)q, (const T*)k_slab, (const T*)v_slab, req_to_token,
                                                      pt_stride, req_pool_indices, prefix_lens, qo_indptr, req_order,
-                                                     batch, n_q_heads, n_kv_heads, scale_log2, (T*)out);
+                                                     batch, n_q_heads, n_kv_heads, scale_log2, (T*)out, total_vb);
   return check_launch("extend_attention_kernel");
 }
 
