@@ -154,7 +154,8 @@ int bsgl_merge_partials(const float* part_o, const float* part_lse, const int32_
  * q rows are packed in request order (qo_indptr); request i's row r sees KV columns
  * 0..prefix_lens[i]+r of req_to_token[req_pool_indices[i], :seq_lens[i]].  req_order (int32 [B], a
  * permutation of 0..B-1, NULL = identity) is the order in which requests are handed to the SMs;
- * K4's heavy_order (longest KV first) shortens the tail of ragged batches.  It never changes results. */
+ * K4's heavy_order (longest KV first) shortens the tail of ragged batches.  It never changes results.
+ * One persistent CTA per SM walks the (request, KV head, 256-packed-row chunk) work items. */
 int bsgl_extend_attention(const void* q, const void* k_slab, const void* v_slab,
                           const int32_t* req_to_token, int64_t page_table_stride,
                           const int64_t* req_pool_indices, const int64_t* seq_lens,
@@ -241,7 +242,10 @@ int bsgl_slot_ring_push(int32_t* ring, int64_t capacity, int64_t tail, int64_t n
  *   mc_staging / mc_out   NVLS multicast views of the same staging / output regions (every rank's copy behind
  *                         one address), or both NULL: then partial tiles travel by peer stores (two-shot)
  *   timeout_s    a peer that never arrives traps the kernel after this many seconds
- * All ranks must make the same sequence of calls.  hidden % 128 == 0, k_local % 64 == 0, world <= 8. */
+ * All ranks must make the same sequence of calls.  hidden % 128 == 0, k_local % 64 == 0, world <= 8.
+ * Environment (read per call / once): BSGL_K8_GEMM=single|pair forces the GEMM form (128 x 128 single-CTA tiles or
+ * 256 x 256 cta_group::2 pair blocks; default: pairs at world 1 when the tiles exceed one wave),
+ * BSGL_K8_TILE_ORDER=grouped restores round 1's owner-by-owner visiting order.  Neither changes results. */
 int bsgl_comm_alloc(int64_t bytes, void** dev_ptr, void* ipc_handle_64);
 int bsgl_comm_open(const void* ipc_handle_64, void** dev_ptr);
 int bsgl_comm_close(void* dev_ptr);
