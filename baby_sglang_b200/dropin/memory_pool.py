@@ -74,6 +74,8 @@ class BaseTokenToKVPool:
         self._ring: torch.Tensor = None
         self._head = 0
         self._count = 0
+        self._mutations = 0          # bumped by every alloc / free / clear: invalidates the `free_slots` snapshot
+        self._snapshot = None
         self.clear()
 
     # -- queue plumbing ------------------------------------------------------------------
@@ -96,7 +98,14 @@ class BaseTokenToKVPool:
 
     @property
     def free_slots(self) -> torch.Tensor:
-        return self._ordered().cpu()
+        """The queue in FIFO order as a CPU int32 tensor (the reference's attribute; nothing in the reference's
+        scheduler or radix cache reads it -- they use `available_size`, `alloc`, `free`).  Materialising it costs a
+        kernel and a blocking D2H copy, so the copy is kept until the queue changes: a caller that polls it pays once
+        per change, not once per access."""
+        key = (self._head, self._count, id(self._ring), self._mutations)
+        if self._snapshot is None or self._snapshot[0] != key:
+            self._snapshot = (key, self._ordered().cpu())
+        return self._snapshot[1]
 
     # -- reference API -------------------------------------------------------------------
     def available_size(self) -> int:
@@ -115,6 +124,7 @@ class BaseTokenToKVPool:
             picked = torch.cat((self._ring[self._head:], self._ring[: end - cap]))
         self._head = end % cap
         self._count -= need_size
+        self._mutations += 1
         return picked if self._dev_ring else picked.to(self.device, non_blocking=True)
 
     def free(self, free_index: torch.Tensor) -> None:
@@ -139,12 +149,14 @@ class BaseTokenToKVPool:
             if first < n:
                 self._ring[: n - first] = vals[first:]
         self._count += n
+        self._mutations += 1
 
     def clear(self) -> None:
         # slots 1..size; slot 0 is reserved for padded tokens' dummy writes
         self._ring = torch.arange(1, self.size + 1, dtype=torch.int32, device=self.device if self._dev_ring else "cpu")
         self._head = 0
         self._count = self.size
+        self._mutations += 1
 
     def get_key_buffer(self, layer_id: int) -> torch.Tensor:
         raise NotImplementedError()
