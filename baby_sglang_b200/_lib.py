@@ -36,7 +36,7 @@ SIGNATURES = {
     "bsgl_merge_partials": (c_int, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
     "bsgl_rope_kv_store": (c_int, [_p, _l, _p, _p, _p, _p, _p, _l, _p, _l, _i, _i, _i, _i, _p]),
     "bsgl_greedy_sample": (c_int, [_p, _l, _i, _i, _p, _i, _p, _p, _p, _p, _p]),
-    "bsgl_extend_attention": (c_int, [_p, _p, _p, _p, _l, _p, _p, _p, _p, _p, _i, _l, _i, _i, _i, c_float, _i, _p, _p]),
+    "bsgl_extend_attention": (c_int, [_p, _p, _p, _p, _l, _p, _p, _p, _p, _p, _i, _l, _i, _i, _i, c_float, _i, _p, _p, _p]),
     "bsgl_page_table_write_rows": (c_int, [_p, _l, _l, _i, _p, _i, _p, _p, _p]),
     "bsgl_page_table_append": (c_int, [_p, _l, _l, _i, _p, _p, _p, _i, _p]),
     "bsgl_slot_ring_pop": (c_int, [_p, _l, _l, _l, _p, _p]),

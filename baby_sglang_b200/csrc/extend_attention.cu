@@ -94,7 +94,8 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
                         const int32_t* __restrict__ req_to_token, int64_t pt_stride,
                         const int64_t* __restrict__ req_pool_indices, const int64_t* __restrict__ prefix_lens,
                         const int32_t* __restrict__ qo_indptr, const int32_t* __restrict__ req_order, int batch,
-                        int n_q_heads, int n_kv_heads, float scale_log2, T* __restrict__ out, int total_vb) {
+                        int n_q_heads, int n_kv_heads, float scale_log2, T* __restrict__ out, int total_vb,
+                        int32_t* __restrict__ work_counter) {
   using C = ExtCfg<D>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];   // SWIZZLE_128B operand tiles need 1024-byte alignment
   const uint32_t smem_base = smem_u32(smem_raw);
@@ -114,13 +115,39 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
   struct Work {
     int found, req, h, q_begin, prefix, t0, n_tok, kv_end, nkv;
   };
-  // Items come in decreasing cost (dispatch order), so the rounds are dealt boustrophedon: CTA b takes position b of
-  // the even rounds and position G - 1 - b of the odd ones, which evens out the per-CTA totals without a shared counter
-  // (plain round-robin gave CTA 0 the dearest item of every round: 7 % slower than the hardware's greedy block
-  // scheduler on the ragged C3 mix).
-  auto vb_of = [&](int round) {
-    const int g = (int)gridDim.x, b = (int)blockIdx.x;
-    return round * g + ((round & 1) ? g - 1 - b : b);
+  // Items come in decreasing cost (dispatch order).  With a work counter the CTAs draw them greedily (the next item
+  // goes to whichever CTA is free first, like the hardware's block scheduler did for one-item CTAs): producer warp 0
+  // is the dealer -- it runs ahead of the other roles anyway -- and publishes every draw in a small shared-memory
+  // FIFO that the other warps read; no role ever waits for a slower one to read it (the dealer is at most the depth of
+  // the K/V ring ahead, the FIFO holds 8 draws).  Without a counter the rounds are dealt boustrophedon: CTA b takes
+  // position b of the even rounds and position G - 1 - b of the odd ones (plain round-robin gave CTA 0 the dearest
+  // item of every round: 7 % slower on the ragged C3 mix).
+  volatile int* deal_fifo = reinterpret_cast<volatile int*>(smem + C::MISC_OFF + 16);   // [8]
+  volatile int* deal_pub = reinterpret_cast<volatile int*>(smem + C::MISC_OFF + 48);    // draws published so far
+  const bool is_dealer = warp == kExtMmaWarp + 1;
+  auto vb_of = [&](int round) -> int {
+    if (work_counter == nullptr) {
+      const int g = (int)gridDim.x, b = (int)blockIdx.x;
+      return round * g + ((round & 1) ? g - 1 - b : b);
+    }
+    int vb = 0;
+    if (is_dealer) {
+      if (lane == 0) {
+        vb = atomicAdd(work_counter, 1);
+        deal_fifo[round & 7] = vb;
+        __threadfence_block();
+        *deal_pub = round + 1;
+      }
+      vb = __shfl_sync(0xffffffffu, vb, 0);
+    } else {
+      if (lane == 0) {
+        while (*deal_pub <= round) __nanosleep(64);
+        __threadfence_block();
+        vb = deal_fifo[round & 7];
+      }
+      vb = __shfl_sync(0xffffffffu, vb, 0);
+    }
+    return vb;
   };
   auto find_work = [&](int vb) {
     Work w;
@@ -173,6 +200,7 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
   const uint32_t o_full = q_free + 8;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::MISC_OFF);
   if (threadIdx.x == 0) {
+    *reinterpret_cast<volatile int*>(smem + C::MISC_OFF + 48) = 0;     // no work item dealt yet
     mbar_init(q_full, kExtProducerThreads);       // one cp.async-completion arrive per producer thread
     mbar_init(q_free, 1);                         // tcgen05.commit
     mbar_init(o_full, 1);                         // tcgen05.commit
@@ -544,6 +572,15 @@ extend_attention_kernel(const T* __restrict__ q, const T* __restrict__ k_slab, c
 
   // ---- teardown: every TMEM read is done before the allocation is released
   __syncthreads();
+  if (work_counter != nullptr && threadIdx.x == 0) {
+    // the last CTA to get here returns the counter pair to zero for the next launch (every CTA has stopped drawing)
+    __threadfence();
+    if (atomicAdd(work_counter + 1, 1) == (int)gridDim.x - 1) {
+      work_counter[0] = 0;
+      work_counter[1] = 0;
+      __threadfence();
+    }
+  }
   if (warp == kExtMmaWarp) {
     tc::fence_after_sync();
     tc::tmem_dealloc(tmem, C::TMEM_COLS);
@@ -559,7 +596,8 @@ template <typename T, int D, int EXPMODE>
 static int launch_extend(const void* q, const void* k_slab, const void* v_slab, const int32_t* req_to_token,
                          int64_t pt_stride, const int64_t* req_pool_indices, const int64_t* prefix_lens,
                          const int32_t* qo_indptr, const int32_t* req_order, int batch, int64_t n_tokens,
-                         int n_q_heads, int n_kv_heads, float sm_scale, void* out, cudaStream_t stream) {
+                         int n_q_heads, int n_kv_heads, float sm_scale, void* out, int32_t* work_counter,
+                         cudaStream_t stream) {
   using C = ExtCfg<D>;
   auto kern = extend_attention_kernel<T, D, EXPMODE>;
   static thread_local int configured_dev = -1;
@@ -588,7 +626,8 @@ static int launch_extend(const void* q, const void* k_slab, const void* v_slab, 
   const float scale_log2 = sm_scale * 1.4426950408889634f;
   kern<<<grid, kExtThreads, C::SMEM_BYTES, stream>>>((const T*)q, (const T*)k_slab, (const T*)v_slab, req_to_token,
                                                      pt_stride, req_pool_indices, prefix_lens, qo_indptr, req_order,
-                                                     batch, n_q_heads, n_kv_heads, scale_log2, (T*)out, total_vb);
+                                                     batch, n_q_heads, n_kv_heads, scale_log2, (T*)out, total_vb,
+                                                     work_counter);
   return check_launch("extend_attention_kernel");
 }
 
@@ -599,7 +638,7 @@ extern "C" int bsgl_extend_attention(const void* q, const void* k_slab, const vo
                                      const int64_t* req_pool_indices, const int64_t* seq_lens,
                                      const int64_t* prefix_lens, const int32_t* qo_indptr,
                                      const int32_t* req_order, int batch, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim, float sm_scale,
-                                     int dtype, void* out, void* stream) {
+                                     int dtype, void* out, int32_t* work_counter, void* stream) {
   using namespace bsgl;
   (void)seq_lens;   // seq = prefix + ext; ext comes from qo_indptr
   BSGL_REQUIRE(batch >= 0 && n_tokens >= 0, "bsgl_extend_attention: negative sizes");
@@ -618,7 +657,8 @@ extern "C" int bsgl_extend_attention(const void* q, const void* k_slab, const vo
   cudaStream_t s = (cudaStream_t)stream;
 #define BSGL_EXT1(T, D, M)                                                                                          \
   return launch_extend<T, D, M>(q, k_slab, v_slab, req_to_token, page_table_stride, req_pool_indices, prefix_lens, \
-                                qo_indptr, req_order, batch, n_tokens, n_q_heads, n_kv_heads, sm_scale, out, s)
+                                qo_indptr, req_order, batch, n_tokens, n_q_heads, n_kv_heads, sm_scale, out, \
+                                work_counter, s)
 #ifdef BSGL_EXT_EXPERIMENTS
   // scripts/ builds only (-DBSGL_EXT_EXPERIMENTS): the other exponential splits and the timing experiments that
   // skip the exponentials (4, 6) or the K/V gather (5, 6) -- the latter give WRONG results by design, which is why

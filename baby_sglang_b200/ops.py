@@ -180,6 +180,7 @@ class BatchMetadata:
     plan: Optional[AttnPlan]
     kv_indices: Optional[torch.Tensor] = None  # int32 [sum(seq)] (built on request)
     heavy_order: Optional[torch.Tensor] = None  # int32 [B] requests by descending seq_len (extend only)
+    work_counter: Optional[torch.Tensor] = None  # int32 [2], zero: K3's work-item dealer (returned to zero by every launch)
     _streams_seen: Optional[set] = None         # streams the buffers are already recorded on
 
     def use_on_current_stream(self) -> None:
@@ -194,7 +195,8 @@ class BatchMetadata:
         if key in self._streams_seen:
             return
         self._streams_seen.add(key)
-        tensors = [self.positions, self.kv_indptr, self.qo_indptr, self.extended_lens, self.kv_indices, self.heavy_order]
+        tensors = [self.positions, self.kv_indptr, self.qo_indptr, self.extended_lens, self.kv_indices, self.heavy_order,
+                   self.work_counter]
         if self.plan is not None:
             tensors += [self.plan.row_idx_off, self.plan.row_kv_len, self.plan.plan_hdr, self.plan.tile_indptr,
                         self.plan.cta_first_seq]
@@ -272,7 +274,8 @@ def build_extend_metadata(req_to_token: torch.Tensor, req_pool_indices: torch.Te
     _count()
     plan = AttnPlan(T, int(n_kv_heads), nhg, n_ctas, row_idx_off, row_kv_len, plan_hdr, tile_indptr,
                     cta_first_seq) if row_plan else None
-    return BatchMetadata(positions, kv_indptr, qo_indptr, extended, plan, heavy_order=heavy_order)
+    return BatchMetadata(positions, kv_indptr, qo_indptr, extended, plan, heavy_order=heavy_order,
+                         work_counter=torch.zeros(2, dtype=torch.int32, device=dev))
 
 
 def gather_kv_indices(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
@@ -362,11 +365,15 @@ def extend_mode(n_tokens: int, batch: int) -> str:
 def extend_attention_tc(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor, req_to_token: torch.Tensor,
                         req_pool_indices: torch.Tensor, seq_lens: torch.Tensor, prefix_lens: torch.Tensor,
                         qo_indptr: torch.Tensor, sm_scale: float, out: Optional[torch.Tensor] = None,
-                        req_order: Optional[torch.Tensor] = None) -> torch.Tensor:
+                        req_order: Optional[torch.Tensor] = None,
+                        work_counter: Optional[torch.Tensor] = None) -> torch.Tensor:
     """K3: ragged extend attention on tcgen05/TMEM (reference `_prefill_attention`,
     attn_backend.py:34-110).  q rows are packed in request order (`qo_indptr`); request i's row r
     sees KV columns 0..prefix_i + r of its page-table row.  `req_order` (K4's `heavy_order`) only
-    changes the order in which requests are dispatched to the SMs, never the result."""
+    changes the order in which requests are dispatched to the SMs, never the result.  `work_counter` (int32 [2],
+    zero; K4's metadata owns one) lets the persistent CTAs draw their work items greedily from a device counter --
+    each launch returns it to zero; without it the items are dealt statically.  Launches that share a counter must be
+    stream-ordered (the layers of one forward are)."""
     dev = _require_cuda(q, k_slab, v_slab, req_to_token, req_pool_indices, seq_lens, prefix_lens, qo_indptr)
     if q.dim() != 3:
         raise _lib.BsglError(f"q must be [tokens, Hq, D], got {tuple(q.shape)}")
@@ -389,11 +396,15 @@ def extend_attention_tc(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Ten
     if req_order is not None and (req_order.dtype != torch.int32 or int(req_order.shape[0]) != B or
                                   not req_order.is_cuda):
         raise _lib.BsglError("req_order must be a CUDA int32 tensor of length batch")
+    if work_counter is not None and (work_counter.dtype != torch.int32 or int(work_counter.numel()) < 2 or
+                                     not work_counter.is_cuda or not work_counter.is_contiguous()):
+        raise _lib.BsglError("work_counter must be a contiguous CUDA int32 tensor of at least 2 elements")
     rc = _lib.load().bsgl_extend_attention(
         q.data_ptr(), k_slab.data_ptr(), v_slab.data_ptr(), req_to_token.data_ptr(), req_to_token.stride(0),
         rpi.data_ptr(), sl.data_ptr(), pl.data_ptr(), qo_indptr.data_ptr(),
         req_order.data_ptr() if req_order is not None else ctypes.c_void_p(0), B, T, Hq, Hkv, D, float(sm_scale),
-        dtype_code(q.dtype), out.data_ptr(), _stream())
+        dtype_code(q.dtype), out.data_ptr(),
+        work_counter.data_ptr() if work_counter is not None else ctypes.c_void_p(0), _stream())
     _lib.check(rc, "bsgl_extend_attention")
     _count()
     return out
@@ -412,7 +423,8 @@ def extend_attention(q: torch.Tensor, k_slab: torch.Tensor, v_slab: torch.Tensor
     mode = mode or extend_mode(int(q.shape[0]), B)
     if mode == "tcgen05":
         return extend_attention_tc(q, k_slab, v_slab, r2t, forward_batch.req_pool_indices, forward_batch.seq_lens,
-                                   forward_batch.prefix_lens, md.qo_indptr, sm_scale, req_order=md.heavy_order)
+                                   forward_batch.prefix_lens, md.qo_indptr, sm_scale, req_order=md.heavy_order,
+                                   work_counter=md.work_counter)
     if md.plan is None:   # metadata was built for the tensor-core path: add the row plan now
         full = build_extend_metadata(r2t, forward_batch.req_pool_indices, forward_batch.seq_lens,
                                      forward_batch.prefix_lens, int(q.shape[0]), int(k_slab.shape[1]),

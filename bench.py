@@ -258,14 +258,14 @@ def measure_extend_c3(device, reps=20):
     out = torch.empty(T, Hq * D, device=device, dtype=dt)
     for _ in range(3):
         ops.extend_attention_tc(q, k_slab, v_slab, r2t, rpi, seq_d, pre_d, md.qo_indptr, D ** -0.5, out=out,
-                                req_order=md.heavy_order)
+                                req_order=md.heavy_order, work_counter=md.work_counter)
     torch.cuda.synchronize()
     times = []
     for _ in range(reps):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         ops.extend_attention_tc(q, k_slab, v_slab, r2t, rpi, seq_d, pre_d, md.qo_indptr, D ** -0.5, out=out,
-                                req_order=md.heavy_order)
+                                req_order=md.heavy_order, work_counter=md.work_counter)
         b.record()
         torch.cuda.synchronize()
         times.append(a.elapsed_time(b))

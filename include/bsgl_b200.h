@@ -155,13 +155,15 @@ int bsgl_merge_partials(const float* part_o, const float* part_lse, const int32_
  * 0..prefix_lens[i]+r of req_to_token[req_pool_indices[i], :seq_lens[i]].  req_order (int32 [B], a
  * permutation of 0..B-1, NULL = identity) is the order in which requests are handed to the SMs;
  * K4's heavy_order (longest KV first) shortens the tail of ragged batches.  It never changes results.
- * One persistent CTA per SM walks the (request, KV head, 256-packed-row chunk) work items. */
+ * One persistent CTA per SM walks the (request, KV head, 256-packed-row chunk) work items.  work_counter: int32 [2],
+ * zero on entry and returned to zero by the launch (the CTAs draw items greedily from it; launches sharing one must be
+ * stream-ordered), or NULL for a static dealing of the items. */
 int bsgl_extend_attention(const void* q, const void* k_slab, const void* v_slab,
                           const int32_t* req_to_token, int64_t page_table_stride,
                           const int64_t* req_pool_indices, const int64_t* seq_lens,
                           const int64_t* prefix_lens, const int32_t* qo_indptr,
                           const int32_t* req_order, int batch, int64_t n_tokens, int n_q_heads, int n_kv_heads, int head_dim,
-                          float sm_scale, int dtype, void* out, void* stream);
+                          float sm_scale, int dtype, void* out, int32_t* work_counter, void* stream);
 
 /* K5 (the step immediately before the path).  RoPE + q/k/v split of the fused
  * projection output + KV store in one launch.  Replaces RotaryEmbedding.forward/_apply_rope

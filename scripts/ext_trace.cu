@@ -54,7 +54,7 @@ int main(int argc, char** argv) {
   cudaMemset(dtrace, 0, 10 * 128 * 8 * 8);
   auto run = [&]() {
     return bsgl_extend_attention(dq, dk, dv, dr2t, C, drpi, nullptr, dpre, dqo, nullptr, B, T, Hq, Hkv, D,
-                                 0.08838834764f, BSGL_BF16, dout, nullptr);
+                                 0.08838834764f, BSGL_BF16, dout, nullptr, nullptr);
   };
   for (int i = 0; i < 3; ++i) run();
   cudaDeviceSynchronize();

@@ -60,6 +60,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--mode", default="tcgen05", choices=["tcgen05", "rowwise"])
     ap.add_argument("--no-order", action="store_true", help="dispatch requests in index order (no heavy-first)")
+    ap.add_argument("--static", action="store_true", help="deal the work items statically (no device work counter)")
     ap.add_argument("--sustain", type=float, default=0.0,
                     help="also launch back to back for this many seconds while nvidia-smi samples SM clock and power")
     ap.add_argument("--lib", default=None, help="load this build of the library instead of the in-tree one "
@@ -78,7 +79,8 @@ def main():
     def run():
         if a.mode == "tcgen05":
             ops.extend_attention_tc(w["q"], w["k_slab"], w["v_slab"], w["r2t"], w["rpi"], seq, pre, md.qo_indptr,
-                                    scale, out=out, req_order=None if a.no_order else md.heavy_order)
+                                    scale, out=out, req_order=None if a.no_order else md.heavy_order,
+                                    **({} if a.static or a.lib else {"work_counter": md.work_counter}))
         else:
             ops.paged_attention(w["q"], w["k_slab"], w["v_slab"], w["r2t"], md.plan, scale, out=out)
 

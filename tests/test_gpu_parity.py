@@ -57,6 +57,14 @@ def _run_backend(ops, c, dtype=torch.bfloat16, n_ctas=None, store=True, extend_m
             plain = ops.extend_attention_tc(q, k_slab, v_slab, r2t, c.req_pool_indices.cuda(), c.seq_lens.cuda(),
                                             c.prefix_lens.cuda(), md.qo_indptr, c.D ** -0.5)
             assert torch.equal(out, plain)
+            # neither does the dealing of the work items to the persistent CTAs: greedy draws from the metadata's
+            # device counter (twice: every launch must hand the counter back as zeros) vs the static dealing above
+            for _ in range(2):
+                drawn = ops.extend_attention_tc(q, k_slab, v_slab, r2t, c.req_pool_indices.cuda(), c.seq_lens.cuda(),
+                                                c.prefix_lens.cuda(), md.qo_indptr, c.D ** -0.5,
+                                                req_order=md.heavy_order, work_counter=md.work_counter)
+                assert torch.equal(out, drawn)
+                assert int(md.work_counter.abs().sum()) == 0
     else:
         md = ops.build_decode_metadata(r2t, c.req_pool_indices.cuda(), c.seq_lens.cuda(), c.Hkv, n_ctas=n_ctas)
         out = ops.paged_attention(q, k_slab, v_slab, r2t, md.plan, c.D ** -0.5)
