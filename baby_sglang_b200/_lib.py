@@ -34,6 +34,8 @@ SIGNATURES = {
     "bsgl_partial_sizes": (c_int, [_i, _i, _i, _i, POINTER(c_int64), POINTER(c_int64)]),
     "bsgl_paged_attention": (c_int, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, c_float, _i, _p, _p, _p, _i, _p]),
     "bsgl_merge_partials": (c_int, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
+    "bsgl_static_scratch_bytes": (c_int, []),
+    "bsgl_paged_attention_static": (c_int, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, c_float, _i, _p, _i, _p]),
     "bsgl_rope_kv_store": (c_int, [_p, _l, _p, _p, _p, _p, _p, _l, _p, _l, _i, _i, _i, _i, _p]),
     "bsgl_greedy_sample": (c_int, [_p, _l, _i, _i, _p, _i, _p, _p, _p, _p, _p]),
     "bsgl_extend_attention": (c_int, [_p, _p, _p, _p, _l, _p, _p, _p, _p, _p, _i, _l, _i, _i, _i, c_float, _i, _p, _p, _p]),

@@ -5,8 +5,10 @@
  * types.  Every entry point returns 0 on success and a non-zero code on failure, in which
  * case bsgl_last_error() (thread-local) describes it.  All device pointers are BORROWED for
  * stream-ordered work only: the library never allocates, frees or retains them, holds no
- * process-global device scratch, and launches on the `stream` it is given (the reference runs
- * this path on a worker thread under a non-default stream, overlap_worker.py:104-106).
+ * process-global device scratch (one exception, opt-in: bsgl_paged_attention_static below keeps
+ * its partials in an 8 MiB array inside the library's device image), and launches on the `stream`
+ * it is given (the reference runs this path on a worker thread under a non-default stream,
+ * overlap_worker.py:104-106).
  *
  * What each entry point replaces in the reference (paths relative to baby-llm/baby-sglang):
  *
@@ -20,6 +22,7 @@
  *                               SDPA, cat) — split-KV partial pass; also
  *                               row-wise extend for short extends          attn_backend.py:34-110
  *   bsgl_merge_partials         (no counterpart: LSE merge of the split-KV partials)
+ *   bsgl_paged_attention_static (no counterpart: K2 + K2c for callers that cannot allocate scratch)
  *   bsgl_extend_attention       _prefill_attention                         attn_backend.py:34-110
  *   bsgl_rope_kv_store          RotaryEmbedding.forward + split + set_kv_buffer qwen2.py:249-290
  *   bsgl_greedy_sample          Scheduler._sample_next_ids (greedy requests)   scheduler.py:509-546, sample.py:19-60
@@ -51,6 +54,7 @@ extern "C" {
 #define BSGL_TILE_TOKENS 16    /* KV tokens per pipeline tile of the paged-attention kernel */
 #define BSGL_MIN_TILES_PER_CTA 16  /* measured: B=1..4 decode 0.82 -> 0.59 ms per 28 layers vs 4 (fewer partials) */
 #define BSGL_PLAN_HDR_INTS 4   /* plan_hdr = { n_tiles, n_ctas_eff, n_seqs, reserved } */
+#define BSGL_STATIC_SCRATCH_BYTES (8 << 20)  /* built-in partials array of bsgl_paged_attention_static, per GPU */
 
 enum bsgl_dtype { BSGL_BF16 = 0, BSGL_F16 = 1, BSGL_F32 = 2 };
 
@@ -149,6 +153,37 @@ int bsgl_merge_partials(const float* part_o, const float* part_lse, const int32_
                         const int32_t* tile_indptr, const int32_t* cta_first_seq, int n_ctas,
                         int n_rows, int n_q_heads, int n_kv_heads, int head_dim, int dtype, void* out,
                         void* stream);
+
+/* K2 + K2c without caller scratch.  NO COUNTERPART IN THE REFERENCE (its attention path allocates freely through
+ * torch); this exists for hosts of the library that cannot allocate device memory where they call it: a serving
+ * worker whose HBM was divided up at start-up (weights, then a KV pool sized to what is left, memory_pool.py's
+ * `size`) and for which a mid-serving cudaMalloc fails or synchronises the whole device under the overlap worker's
+ * second stream; a pass-through C / cgo / JNI binding that owns no device allocator; code in a region that must
+ * not allocate or synchronise at all.
+ *
+ * Same arguments and same results (bit for bit) as bsgl_paged_attention followed by bsgl_merge_partials on the same
+ * stream, except that part_o / part_lse are not passed: the partials live in a BSGL_STATIC_SCRATCH_BYTES (8 MiB)
+ * array that is part of the library's device image.  Things a caller must know:
+ *   - every GPU whose context loads the library holds those 8 MiB until the process exits, used or not;
+ *   - a request whose partials do not fit (bsgl_partial_sizes: (part_o + part_lse) floats * 4, part_o rounded up
+ *     to 256 bytes) returns BSGL_ERR_INVALID with the needed and available byte counts in bsgl_last_error() and
+ *     launches nothing.  148 CTAs need at most 4.8 MiB (32 q heads per group, head_dim 128);
+ *   - the first call on each device resolves the array's device address (cudaGetSymbolAddress with that device
+ *     current; this can make the driver load the module).  Make that first call before starting any stream
+ *     capture on the device.  Later calls only launch the two kernels;
+ *   - it calls no cudaMalloc / cudaFree / allocating library routine;
+ *   - all calls on a device share the array and it keeps the previous call's contents.  Nothing in it needs to be
+ *     zero on entry (the merge reads only what the same call's attention kernel wrote), so nothing is cleared.
+ *     Calls whose kernels may run concurrently on one GPU (unordered streams, two host threads) race on it:
+ *     keep them stream-ordered, or use bsgl_paged_attention with a buffer per stream.
+ * bsgl_static_scratch_bytes() returns the capacity the loaded binary was built with. */
+int bsgl_static_scratch_bytes(void);
+int bsgl_paged_attention_static(const void* q, const void* k_slab, const void* v_slab,
+                                const int32_t* idx_base, const int64_t* row_idx_off,
+                                const int32_t* row_kv_len, const int32_t* plan_hdr,
+                                const int32_t* tile_indptr, const int32_t* cta_first_seq,
+                                int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
+                                float sm_scale, int dtype, void* out, int n_ctas, void* stream);
 
 /* K3.  Ragged extend attention (radix-cache prefix + new tokens) on tcgen05/TMEM tensor cores.
  * q rows are packed in request order (qo_indptr); request i's row r sees KV columns
