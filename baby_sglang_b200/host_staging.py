@@ -89,11 +89,12 @@ class HostStagedAttention:
             q, k, v = self._split(stage[l % 2])
             out = self._backend.forward(q, k, v, layers[l], forward_batch, True)
             if after is not None:
-                # `after` may hand back a view of a buffer it reuses two calls later (K8's output buffers
-                # alternate with the call parity): layer l-2's download must have left it before layer l's call
-                # can overwrite it -- on this rank by a peer's stores too, which follow the peer's own call
-                if l >= 2:
-                    cur.wait_event(copied[l - 2])
+                # `after` may hand back a view of a buffer that its NEXT call overwrites (K8's communicator has a
+                # single output buffer, valid until the following call): layer l-1's download must have left it
+                # before layer l's call starts.  Waiting on this rank's compute stream also holds back the peers'
+                # stores into this rank's buffer, which they issue only after seeing this rank enter call l.
+                if l >= 1:
+                    cur.wait_event(copied[l - 1])
                 out = after(out)
             done[l].record(cur)
             out.record_stream(self.d2h)

@@ -111,9 +111,74 @@ def run(mode, rank, world, group):
     return ok
 
 
+def host_staged(rank, world, group):
+    """HostStagedAttention with `after` = K8 (bench.py's TP e2e leg): every layer's downloaded result must equal the
+    resident path's.  K8 has ONE output buffer, so layer l+1's call may only start once layer l's download has left
+    it; the download (10 MiB per layer over PCIe) is far slower than a layer of this tiny attention, so a missing
+    dependency shows up as layer l+1's tiles inside out_host[l]."""
+    import attn_backend
+    import forward_batch
+    import memory_pool
+    from baby_sglang_b200.host_staging import HostStagedAttention
+    os.environ["BSGL_K8_EXCHANGE"] = ""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    B, Hq, Hkv, D, L, hidden, ctx = 1024, 8, 2, 128, 6, 5120, 24
+    dt = torch.bfloat16
+    g = torch.Generator(device="cpu").manual_seed(77 + rank)
+    S = B * ctx
+    kv = memory_pool.MHATokenToKVPool(size=S, dtype=dt, head_num=Hkv, head_dim=D, layer_num=L, device=dev)
+    for l in range(L):
+        kv.k_buffer[l].copy_(torch.randn(S + 1, Hkv, D, generator=g).to(dt))
+        kv.v_buffer[l].copy_(torch.randn(S + 1, Hkv, D, generator=g).to(dt))
+    r2t = memory_pool.ReqToTokenPool(size=B, max_context_len=ctx + 4, device=dev)
+    r2t.req_to_token[:, :ctx] = (torch.arange(S, dtype=torch.int32).view(B, ctx) + 1).to(dev)
+    rpi = torch.arange(B, dtype=torch.int64, device=dev)
+    seq = torch.full((B,), ctx, dtype=torch.int64, device=dev)
+    loc = r2t.req_to_token[:, ctx - 1].contiguous()
+    fb = forward_batch.SimplifiedForwardBatch.create_decode_batch(
+        input_ids=torch.zeros(B, dtype=torch.int64, device=dev), req_pool_indices=rpi, seq_lens=seq,
+        out_cache_loc=loc, req_to_token_pool=r2t, token_to_kv_pool=kv)
+    layers = [type("Layer", (), dict(layer_id=l, head_dim=D, scaling=D ** -0.5))() for l in range(L)]
+    w_o = [(torch.randn(hidden, Hq * D, generator=g) * 0.05).to(dev, dt) for _ in range(L)]
+    qkv_host = [torch.randn(B, (Hq + 2 * Hkv) * D, generator=g).to(dt).pin_memory() for _ in range(L)]
+    comm = tp_runtime.FusedOProjAllReduce(rank, world, group, hidden=hidden, max_tokens=B)
+    staged = HostStagedAttention(Hq, Hkv, D, dev)
+    # resident path: same backend call, K8 output cloned before the next call reuses the buffer
+    want = []
+    for l in range(L):
+        q, k, v = staged._split(qkv_host[l].to(dev))
+        want.append(comm(attn_backend.SimpleAttentionBackend.forward(q, k, v, layers[l], fb, True), w_o[l]).clone())
+    torch.cuda.synchronize()
+    calls = [0]
+
+    def after(out):
+        calls[0] += 1
+        return comm(out, w_o[(calls[0] - 1) % L])
+
+    good = True
+    bad_layers = []
+    for rep in range(3):
+        out_host = [torch.zeros(B, hidden, dtype=dt).pin_memory() for _ in range(L)]
+        staged.forward_layers(qkv_host, out_host, layers, fb, after=after)
+        for l in range(L):
+            if not torch.equal(out_host[l], want[l].cpu()):
+                good = False
+                bad_layers.append((rep, l))
+    flag = torch.tensor([1 if good else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    if rank == 0:
+        print(json.dumps({"case": f"host-staged attention + K8, {L} layers x 3 steps, T={B} hidden={hidden}",
+                          "world": world, "every_layer_download_equals_resident": bool(flag.item()),
+                          "bad_layers_rank0": bad_layers[:6], "ok": bool(flag.item())}), flush=True)
+    comm.close()
+    dist.barrier(group=group)
+    return bool(flag.item())
+
+
 def main():
     rank, world, group = tp_runtime.init_tp()
     ok = run("", rank, world, group)
+    ok &= host_staged(rank, world, group)
     if world > 1:
         ok &= run("nvls", rank, world, group)     # falls back to peer stores where multicast is unavailable
     dist.destroy_process_group()
