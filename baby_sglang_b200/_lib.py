@@ -47,6 +47,7 @@ SIGNATURES = {
     "bsgl_comm_open": (c_int, [_p, POINTER(c_void_p)]),
     "bsgl_comm_close": (c_int, [_p]),
     "bsgl_comm_free": (c_int, [_p]),
+    "bsgl_oproj_flag_bytes": (c_int, [_i, _i, POINTER(c_int64)]),
     "bsgl_oproj_allreduce": (c_int, [_p, _l, _p, _l, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _i, _i, _l,
                                       ctypes.c_double, _i, _p]),
 }

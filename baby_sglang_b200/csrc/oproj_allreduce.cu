@@ -599,6 +599,7 @@ static int launch_oproj(const CUtensorMap& ta, const CUtensorMap& tb, const Opro
   int dev = 0, sms = 0;
   BSGL_CUDA_TRY(cudaGetDevice(&dev));
   BSGL_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  if (sms > 256) sms = 256;   // the flag block reserves 256 per-CTA timestamp records (bsgl_oproj_flag_bytes)
   const int n_mt = (M + kOpBM - 1) / kOpBM, n_nt = N / kOpBN, n_tiles = n_mt * n_nt;
   // Visiting order of the peer-store path.  "global" (default): every rank walks the tiles in the same order, so
   // the `world` partials of a tile reach its owner at about the same time and the owner's reduction trails the
@@ -688,6 +689,15 @@ extern "C" int bsgl_comm_close(void* dev_ptr) {
 extern "C" int bsgl_comm_free(void* dev_ptr) {
   using namespace bsgl;
   if (dev_ptr) BSGL_CUDA_TRY(cudaFree(dev_ptr));
+  return BSGL_OK;
+}
+
+extern "C" int bsgl_oproj_flag_bytes(int max_slots, int max_tiles, int64_t* bytes) {
+  using namespace bsgl;
+  BSGL_REQUIRE(max_slots > 0 && max_tiles > 0 && bytes != nullptr, "bsgl_oproj_flag_bytes: bad arguments");
+  // must match the kernel's `trace` address: flag words rounded up to 1024 bytes, then 256 CTA records of 32 bytes
+  const int64_t words = (int64_t)max_slots * kOpMaxWorld + max_tiles + 2;
+  *bytes = ((words * 4 + 1023) & ~(int64_t)1023) + 256 * 32;
   return BSGL_OK;
 }
 

@@ -23,6 +23,7 @@ The attention path shards only along its natural, exchange-free axes (SURVEY.md 
 from __future__ import annotations
 
 import copy
+import ctypes
 import os
 from dataclasses import dataclass
 from typing import List, Sequence, Tuple
@@ -178,6 +179,11 @@ class FusedOProjAllReduce:
         self._n_flag_words = self.max_slots * 8 + self.max_tiles + 2
         self._off_trace = self._off_flags + up(self._n_flag_words * 4)              # 8-byte aligned
         self.nbytes = self._off_trace + up(256 * 4 * 8)
+        need = ctypes.c_int64(0)
+        ops._lib.check(ops._lib.load().bsgl_oproj_flag_bytes(self.max_slots, self.max_tiles, ctypes.byref(need)),
+                       "bsgl_oproj_flag_bytes")
+        if self.nbytes - self._off_flags < need.value:
+            raise RuntimeError("flag block smaller than the kernel's layout (bsgl_oproj_flag_bytes)")
         self._mine = None
         self._peers = []
         self._symm = None

@@ -272,10 +272,16 @@ int bsgl_slot_ring_push(int32_t* ring, int64_t capacity, int64_t tail, int64_t n
  *   staging_ptrs [world]  every rank's staging buffer as mapped here: world * max_slots * 32 KiB
  *   out_ptrs     [world]  every rank's output buffer (out_bytes); this rank reads its own at out_ptrs[rank]
  *                         after the call (stream-ordered); valid until the rank's next call
- *   flag_ptrs    [world]  every rank's flags: (max_slots * 8 + max_tiles + 2) uint32, zero-initialised, followed by
- *                         148 x 4 uint64 of per-CTA phase timestamps (diagnostics); words max_slots*8 + max_tiles
- *                         (+1) of a rank's own flags are the call counter (epoch) and a CTA counter, kept in
- *                         device memory so that a captured CUDA graph numbers its calls like eager launches
+ *   flag_ptrs    [world]  every rank's flag block, zero-initialised, bsgl_oproj_flag_bytes(max_slots, max_tiles)
+ *                         bytes, laid out exactly as:
+ *                           [0, W*4)            W = max_slots * 8 + max_tiles + 2 uint32 flag words; words W-2 and W-1
+ *                                               of a rank's own block are the call counter (epoch) and a CTA counter,
+ *                                               kept in device memory so that a captured CUDA graph numbers its
+ *                                               calls like eager launches
+ *                           [R, R + 256*32)     R = W*4 rounded UP to a multiple of 1024: one 4 x uint64 record of
+ *                                               phase timestamps per CTA, written by EVERY call at R + 32*blockIdx.x
+ *                                               (the grid never exceeds the SM count; 256 rows are reserved)
+ *                         a block smaller than that is written out of bounds: size it with the query, not by hand
  *   mc_staging / mc_out   NVLS multicast views of the same staging / output regions (every rank's copy behind
  *                         one address), or both NULL: then partial tiles travel by peer stores (two-shot)
  *   timeout_s    a peer that never arrives traps the kernel after this many seconds
@@ -287,6 +293,7 @@ int bsgl_comm_alloc(int64_t bytes, void** dev_ptr, void* ipc_handle_64);
 int bsgl_comm_open(const void* ipc_handle_64, void** dev_ptr);
 int bsgl_comm_close(void* dev_ptr);
 int bsgl_comm_free(void* dev_ptr);
+int bsgl_oproj_flag_bytes(int max_slots, int max_tiles, int64_t* bytes);
 int bsgl_oproj_allreduce(const void* a, int64_t lda, const void* w, int64_t ldw, int n_tokens, int hidden,
                          int k_local, int rank, int world, void* const* staging_ptrs,
                          void* const* out_ptrs, void* const* flag_ptrs, void* mc_staging, void* mc_out,
