@@ -15,7 +15,7 @@ from . import LIB_PATH
 BF16, F16, F32 = 0, 1, 2
 TILE_TOKENS = 16
 PLAN_HDR_INTS = 4
-MIN_TILES_PER_CTA = 16     # BSGL_MIN_TILES_PER_CTA in the header
+MIN_TILES_PER_CTA = 16     # BSGL_MIN_TILES_PER_CTA in the header (bsgl_min_tiles_per_cta() gives the effective value)
 
 _i = c_int
 _l = c_int64
@@ -27,6 +27,7 @@ SIGNATURES = {
     "bsgl_last_error": (c_char_p, []),
     "bsgl_sm_count": (c_int, [POINTER(c_int)]),
     "bsgl_heads_per_group": (c_int, [_i]),
+    "bsgl_min_tiles_per_cta": (c_int, []),
     "bsgl_kv_store": (c_int, [_p, _p, _l, _p, _p, _p, _l, _i, _i, _l, _l, _l, _l, _i, _i, _p]),
     "bsgl_build_decode_metadata": (c_int, [_l, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "bsgl_build_extend_metadata": (c_int, [_l, _p, _p, _p, _i, _l, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),

@@ -84,6 +84,9 @@ __global__ void __launch_bounds__(kSampleThreads) greedy_sample_kernel(
   const int splits = (int)gridDim.x;                         // == cluster size: the CTAs of one vocabulary row
   const int part = (int)blockIdx.x;                          // == rank in the cluster
   const int r = blockIdx.y;
+  // Shared memory of another CTA may only be touched once that CTA is known to have started: every thread
+  // arrives here and waits just before the remote stores below, so the barrier's latency hides behind the scan.
+  cluster.barrier_arrive();
   const int64_t row = qo_indptr ? (int64_t)qo_indptr[r + 1] - 1 : r;   // last token of the request
   const T* src = logits + row * row_stride;
   constexpr int VEC = LogitIo<T>::kVec;
@@ -172,6 +175,7 @@ __global__ void __launch_bounds__(kSampleThreads) greedy_sample_kernel(
   __shared__ int ci[kSampleMaxSplits];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane == 0) { wv[warp] = best; wi[warp] = best_i; }
+  cluster.barrier_wait();                                    // all CTAs of the row are running (arrived at entry)
   __syncthreads();
   if (warp == 0) {
     best = lane < kSampleThreads / 32 ? wv[lane] : -INFINITY;

@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(256) gather_kv_indices_kernel(const int32_t* _
 }
 
 // A CTA of the split-KV kernel gets at least this many 16-token tiles, so short batches use fewer CTAs and their
-// sequences are cut into fewer partials.  BSGL_MIN_TILES_PER_CTA (4) is the measured default; the environment
+// sequences are cut into fewer partials.  BSGL_MIN_TILES_PER_CTA (16) is the measured default; the environment
 // variable of the same name overrides it for tuning runs (read once).
 static int min_tiles_per_cta() {
   static const int v = [] {
@@ -222,6 +222,8 @@ static int min_tiles_per_cta() {
 }  // namespace bsgl
 
 extern "C" {
+
+int bsgl_min_tiles_per_cta(void) { return bsgl::min_tiles_per_cta(); }
 
 int bsgl_build_decode_metadata(int64_t page_table_stride, const int64_t* req_pool_indices, const int64_t* seq_lens,
                                int batch, int n_head_groups, int n_ctas, int64_t* positions, int32_t* kv_indptr,

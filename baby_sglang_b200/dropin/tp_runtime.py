@@ -222,7 +222,12 @@ class FusedOProjAllReduce:
 
     # -- memory ------------------------------------------------------------------------------------------
     def _alloc_symmetric(self):
-        """torch symmetric memory: same-size buffer on every rank, peer-mapped, plus the multicast mapping."""
+        """torch symmetric memory: same-size buffer on every rank, peer-mapped, plus the multicast mapping.
+        Every rank leaves this function with the SAME answer: each computes a local verdict, then ONE all-reduce
+        (outside the try, so that failing and succeeding ranks issue the same collective) decides for the group
+        whether symmetric memory is used at all and whether the multicast mapping is.  (`rendezvous` is itself a
+        collective: a rank that fails before reaching it -- an import error -- fails on every rank alike.)"""
+        ok, base, mc, t, hdl = 1, None, 0, None, None
         try:
             import torch.distributed._symmetric_memory as symm_mem
             t = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=self.device)
@@ -233,19 +238,16 @@ class FusedOProjAllReduce:
             mc = int(hdl.multicast_ptr) if getattr(hdl, "has_multicast_support", False) else 0
             if len(base) != self.world or base[self.rank] != t.data_ptr():
                 raise RuntimeError("unexpected symmetric-memory pointer table")
-            flag = torch.tensor([1 if mc else 0], device=self.device)
-            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)     # all ranks or none
-            mc = mc if int(flag.item()) else 0
-            self._symm = (t, hdl)
-            return base, mc
-        except Exception as e:   # older torch / no fabric: fall back to cudaMalloc + IPC
+        except Exception as e:   # older torch / no fabric: the group falls back to cudaMalloc + IPC
             self._symm_error = repr(e)
-            ok = torch.tensor([0], device=self.device)
-            try:
-                dist.all_reduce(ok, group=self.group)
-            except Exception:
-                pass
+            ok, mc = 0, 0
+        verdict = torch.tensor([ok, 1 if mc else 0], device=self.device)
+        dist.all_reduce(verdict, op=dist.ReduceOp.MIN, group=self.group)     # all ranks or none
+        all_ok, all_mc = (int(x) for x in verdict.tolist())
+        if not all_ok:
             return None, 0
+        self._symm = (t, hdl)
+        return base, (mc if all_mc else 0)
 
     def _alloc_ipc(self):
         ops = self._ops

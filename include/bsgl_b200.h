@@ -73,6 +73,9 @@ int bsgl_sm_count(int* out_sm_count);
 /* KV heads one CTA of the paged-attention kernel handles (the "head group" width) for a pool
  * with n_kv_heads heads: the largest of {4,2,1} dividing n_kv_heads. */
 int bsgl_heads_per_group(int n_kv_heads);
+/* The value the split-KV plans are built with: BSGL_MIN_TILES_PER_CTA unless the environment variable of the same
+ * name (read once per process, for tuning runs) overrides it. */
+int bsgl_min_tiles_per_cta(void);
 
 /* K1.  slab[loc[t], h, :] = src[t, h, :] for K and V in one launch.  Source rows may be
  * strided views (the reference hands `v` as a view of the fused QKV output, qwen2.py:285-290):

@@ -37,6 +37,10 @@ def test_version_and_host_queries(lib):
     assert lib.bsgl_version() == 100
     assert [lib.bsgl_heads_per_group(h) for h in (1, 2, 3, 4, 6, 8, 12)] == [1, 2, 1, 4, 2, 4, 4]
     import ctypes
+    env = os.environ.get("BSGL_MIN_TILES_PER_CTA")
+    assert lib.bsgl_min_tiles_per_cta() == (max(1, int(env)) if env and int(env) >= 1 else _lib.MIN_TILES_PER_CTA)
+    n = ctypes.c_int64()
+    assert lib.bsgl_oproj_flag_bytes(10, 40, ctypes.byref(n)) == 0 and n.value == 1024 + 256 * 32
     o, l = ctypes.c_int64(), ctypes.c_int64()
     assert lib.bsgl_partial_sizes(148, 28, 4, 128, ctypes.byref(o), ctypes.byref(l)) == 0
     assert o.value == 2 * 148 * 28 * 128 and l.value == 2 * 148 * 28

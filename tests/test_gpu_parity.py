@@ -329,7 +329,7 @@ def test_decode_metadata_bit_exact(ops, nhg_heads, n_ctas):
     n_eff = hdr[1]
     tile_indptr, begins, first = O.split_plan(seq.tolist(), nhg, 16, n_eff)
     assert hdr[0] == tile_indptr[-1] and hdr[2] == B * nhg
-    assert n_eff == max(1, min(n_ctas, tile_indptr[-1] // _lib.MIN_TILES_PER_CTA))
+    assert n_eff == max(1, min(n_ctas, tile_indptr[-1] // _lib.load().bsgl_min_tiles_per_cta()))
     assert md.plan.tile_indptr.cpu().tolist() == tile_indptr
     assert md.plan.cta_first_seq.cpu().tolist()[: n_eff + 1] == first
 
