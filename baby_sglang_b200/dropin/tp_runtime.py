@@ -367,11 +367,15 @@ def _mlp_modules(model: torch.nn.Module):
             yield m
 
 
-def shard_mlp(model: torch.nn.Module, rank: int, world_size: int, tp_group) -> int:
+def shard_mlp(model: torch.nn.Module, rank: int, world_size: int, tp_group,
+              fused_allreduce: "FusedOProjAllReduce" = None) -> int:
     """Tensor-parallel SwiGLU MLP (second half), on the unchanged model: rank r keeps
     intermediate columns [r*I/t, (r+1)*I/t) -- rows `cat(gate_shard, up_shard)` of the fused gate/up weight, so the
     reference's `chunk(2, dim=-1)` (qwen2.py:221) still separates gate from up -- and the matching input columns of
-    `down_proj` (bias-free, qwen2.py:206), whose partial output is SUM all-reduced by a forward hook.  Returns the
+    `down_proj` (bias-free, qwen2.py:206), whose partial output is SUM all-reduced: by K8 when a communicator is
+    given (`down_proj` is the same `[T, K_r] . [hidden, K_r]^T` + SUM as `o_proj`, so the layer's second collective
+    rides the same fused kernel; the view it returns is consumed by the next layer's residual add before the next
+    K8 call, qwen2.py:113-121), else by a forward hook on NCCL.  Returns the
     per-rank intermediate size (0 if nothing was sharded: world 1, no MLP modules, or I % world != 0)."""
     if world_size <= 1:
         return 0
@@ -393,20 +397,33 @@ def shard_mlp(model: torch.nn.Module, rank: int, world_size: int, tp_group) -> i
             down.in_features = per_rank
         if hasattr(m.gate_up_proj, "intermediate_size"):
             m.gate_up_proj.intermediate_size = per_rank
-        down.register_forward_hook(lambda _mod, _inp, out, g=tp_group: tp_all_reduce_sum(out, g))
+        if fused_allreduce is not None and per_rank % 64 == 0 and down.out_features == fused_allreduce.hidden \
+                and down.bias is None:
+            down.forward = _fused_oproj_forward(down, fused_allreduce, tp_group)
+        else:
+            down.register_forward_hook(lambda _mod, _inp, out, g=tp_group: tp_all_reduce_sum(out, g))
     return per_rank
 
 
-def _fused_oproj_forward(o_proj: torch.nn.Linear, comm: "FusedOProjAllReduce", tp_group):
-    """`o_proj.forward` replacement: K8 for batches the communicator was sized for, the NCCL pair otherwise."""
+def _fused_oproj_forward(lin: torch.nn.Linear, comm: "FusedOProjAllReduce", tp_group):
+    """`forward` replacement for a bias-free row-parallel linear (`o_proj`, `down_proj`): K8 in place of
+    `F.linear` + `tp_all_reduce_sum`.  Batches larger than the communicator was sized for (a 16 K-token prefill
+    against a decode-sized `max_tokens`) run as consecutive `max_tokens`-row blocks, each copied out of the
+    communicator's single output buffer before the next block's call reuses it; every rank cuts the same blocks
+    (the token count is the same on all ranks), so the call sequence stays identical across the group."""
     def forward(x: torch.Tensor) -> torch.Tensor:
         lead = x.shape[:-1]
         x2 = x.reshape(-1, x.shape[-1])
-        if x2.shape[0] > comm.max_tokens:
-            return tp_all_reduce_sum(torch.nn.functional.linear(x, o_proj.weight), tp_group)
         if not x2.is_contiguous():
             x2 = x2.contiguous()
-        return comm(x2, o_proj.weight).view(*lead, comm.hidden)
+        T, cap = int(x2.shape[0]), comm.max_tokens
+        if T <= cap:
+            return comm(x2, lin.weight).view(*lead, comm.hidden)
+        out = torch.empty((T, comm.hidden), dtype=x2.dtype, device=x2.device)
+        for lo in range(0, T, cap):
+            hi = min(T, lo + cap)
+            out[lo:hi].copy_(comm(x2[lo:hi], lin.weight))
+        return out.view(*lead, comm.hidden)
     return forward
 
 

@@ -222,7 +222,7 @@ def build(shadow_dir: Optional[str], cfg_kwargs: dict, device: str, dtype: torch
         if plan.mode != "kv_head_tp":
             raise ValueError(f"geometry does not shard over {tp['world']} ranks: {plan}")
         if tp.get("mlp"):
-            tpr.shard_mlp(model, tp["rank"], tp["world"], tp["group"])
+            tpr.shard_mlp(model, tp["rank"], tp["world"], tp["group"], fused_allreduce=comm)
         model.config = tpr.kv_pool_config(model.config, plan)      # scheduler.py:50-57 reads num_key_value_heads
     sched = st.scheduler.Scheduler(model, tokenizer=None)
     log = SampleLog()

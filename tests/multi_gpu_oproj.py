@@ -175,10 +175,52 @@ def host_staged(rank, world, group):
     return bool(flag.item())
 
 
+def chunked(rank, world, group):
+    """Batches larger than the communicator: `_fused_oproj_forward` cuts them into max_tokens-row blocks (one row
+    over, a ragged tail, a 16 K-token prefill) instead of leaving K8 for F.linear + NCCL."""
+    os.environ["BSGL_K8_EXCHANGE"] = ""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    hidden, K, cap = 3584, 3584 // world // 128 * 128, 1024
+    comm = tp_runtime.FusedOProjAllReduce(rank, world, group, hidden=hidden, max_tokens=cap)
+    g = torch.Generator(device="cpu").manual_seed(4242 + rank)
+    lin = torch.nn.Linear(K, hidden, bias=False, device=dev, dtype=torch.bfloat16)
+    with torch.no_grad():
+        lin.weight.copy_((torch.randn(hidden, K, generator=g) * 0.05).to(dev, torch.bfloat16))
+    fwd = tp_runtime._fused_oproj_forward(lin, comm, group)
+    ok = True
+    for T in (cap, cap + 1, 2 * cap + 333, 16384):
+        a = torch.randn(T, K, generator=g).to(dev, torch.bfloat16)
+        calls0 = comm.calls
+        with torch.no_grad():
+            out = fwd(a.view(1, T, K))
+            # the same rows through single calls of at most `cap` rows: blocks must reproduce them bit for bit
+            want = torch.cat([comm(a[lo:lo + cap], lin.weight).clone() for lo in range(0, T, cap)])
+            ref = torch.nn.functional.linear(a, lin.weight)
+        n_calls = (comm.calls - calls0) // 2
+        dist.all_reduce(ref, group=group)
+        gathered = [torch.empty_like(out) for _ in range(world)]
+        dist.all_gather(gathered, out.contiguous(), group=group)
+        same = all(torch.equal(gathered[0], t) for t in gathered)
+        exact = bool(torch.equal(out.view(T, hidden), want))
+        err = (out.view(T, hidden).float() - ref.float()).abs().max().item()
+        tol = 2.0 ** -6 * ref.float().abs().max().item() * (1 + world / 4)
+        good = same and exact and tuple(out.shape) == (1, T, hidden) and n_calls == -(-T // cap) and err <= tol
+        ok &= good
+        if rank == 0:
+            print(json.dumps({"case": f"row blocks: T={T} max_tokens={cap} hidden={hidden} K/rank={K}", "world": world,
+                              "k8_calls": n_calls, "bit_identical_across_ranks": same,
+                              "equal_to_blockwise_single_calls": exact, "max_abs_err_vs_nccl_pair": err, "tol": tol,
+                              "ok": good}), flush=True)
+    comm.close()
+    dist.barrier(group=group)
+    return ok
+
+
 def main():
     rank, world, group = tp_runtime.init_tp()
     ok = run("", rank, world, group)
     ok &= host_staged(rank, world, group)
+    ok &= chunked(rank, world, group)
     if world > 1:
         ok &= run("nvls", rank, world, group)     # falls back to peer stores where multicast is unavailable
     dist.destroy_process_group()

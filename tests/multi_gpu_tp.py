@@ -5,7 +5,8 @@ qwen2 model, sharded by the drop-in `tp_runtime` (`shard_attention_heads`, `kv_p
     python -m torch.distributed.run --nnodes=1 --nproc-per-node {2,4,8} --master-addr 127.0.0.1 \
         --master-port 29521 tests/multi_gpu_tp.py
 
-Per variant (o_proj all-reduce by NCCL / by K8 / K8 + TP MLP), cold run + radix-hit rerun, 32 greedy tokens,
+Per variant (o_proj all-reduce by NCCL / by K8 / K8 + TP MLP with down_proj on K8 too / the same with a communicator
+smaller than the prefill, i.e. K8 in row blocks), cold run + radix-hit rerun, 32 greedy tokens,
 teacher-forced with the unsharded run's tokens:
   * index state (page table, KV free-slot FIFO, free rows, radix sizes) bit-exact with the unsharded run's;
   * every rank's own argmax at every step equal to the unsharded token, except at ties: the unsharded side's
@@ -65,9 +66,18 @@ def main():
     ref_runs = _run(base, prompts)
     del base
     ok = True
-    for name, fused, mlp in (("nccl", False, False), ("k8", True, False), ("k8+tp_mlp", True, True)):
+    # the last variant sizes the communicator BELOW the 1 211-token prefill: o_proj and down_proj then run K8 in
+    # 500-row blocks (500 + 500 + 211) instead of leaving the fused path
+    for name, fused, mlp, cap in (("nccl", False, False, 2048), ("k8", True, False, 2048),
+                                  ("k8+tp_mlp", True, True, 2048), ("k8+tp_mlp, 500-row blocks", True, True, 500)):
         run = ref_stack.build(DROPIN_DIR, CFG, "cuda", torch.bfloat16, **POOL, listen=False,
-                              tp=dict(rank=rank, world=world, group=group, fused=fused, mlp=mlp, max_tokens=2048))
+                              tp=dict(rank=rank, world=world, group=group, fused=fused, mlp=mlp, max_tokens=cap))
+        if fused:       # no library GEMM + NCCL pair left on the TP layer path
+            fwd = [m.o_proj.forward for m in run.scheduler.model.modules() if hasattr(m, "o_proj")]
+            assert fwd and all(getattr(f, "__name__", "") == "forward" and not hasattr(f, "__self__") for f in fwd)
+            if mlp:
+                fwd = [m.down_proj.forward for m in run.scheduler.model.modules() if hasattr(m, "down_proj")]
+                assert fwd and all(not hasattr(f, "__self__") for f in fwd), "down_proj is not on K8"
         assert run.scheduler.token_to_kv_pool.head_num == CFG["num_key_value_heads"] // world
         runs = _run(run, prompts, forced=[r["ids"] for r in ref_runs])
         line = {"variant": name, "world": world, "exchange": getattr(run.comm, "last_exchange", "nccl all_reduce")}
