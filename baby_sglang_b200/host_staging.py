@@ -58,10 +58,12 @@ class HostStagedAttention:
 
     @torch.no_grad()
     def forward_layers(self, qkv_host: Sequence[torch.Tensor], out_host: Sequence[torch.Tensor], layers,
-                       forward_batch, after=None) -> None:
+                       forward_batch, after=None, out_rows=None) -> None:
         """One step: every layer's attention, uploads and downloads overlapped with compute.
         `after(out)` (optional) post-processes a layer's device output before it is downloaded.
-        Returns once `out_host` is complete."""
+        `out_rows = (lo, hi)` downloads only rows lo..hi-1 of each layer's result into `out_host[l]` (under tensor
+        parallelism the all-reduced result is replicated: each rank then brings home its 1/N of the rows instead of
+        every rank downloading all of them).  Returns once `out_host` is complete."""
         L = len(layers)
         if len(qkv_host) != L or len(out_host) != L:
             raise RuntimeError("qkv_host / out_host / layers must have one entry per layer")
@@ -101,7 +103,7 @@ class HostStagedAttention:
             keep.append(out)
             with torch.cuda.stream(self.d2h):
                 self.d2h.wait_event(done[l])
-                out_host[l].copy_(out, non_blocking=True)
+                out_host[l].copy_(out if out_rows is None else out[out_rows[0]:out_rows[1]], non_blocking=True)
                 copied[l].record(self.d2h)
         cur.wait_stream(self.d2h)
         cur.synchronize()                  # the caller reads out_host next

@@ -81,15 +81,27 @@ def tensor_peak():
     return 1590.0, "fallback (B200_PROFILING.md 1.59 PFLOP/s)"
 
 
-def traffic_from_profiles(key):
-    """dram bytes per launch of the dominant kernel, from the committed ncu --set full capture (or None)."""
-    for name in ("r2_traffic.json", "r1_traffic.json"):
+def traffic_from_profiles(key, with_source=False):
+    """dram bytes per launch of the dominant kernel, from the committed ncu --set full capture (or None).  The figure
+    is a CAPTURE, not something this run measured: `with_source` also returns where it came from (file, the capture
+    it summarises, the commit that last touched the file) so that a stale figure is visible in the line."""
+    for name in ("r3_traffic.json", "r2_traffic.json", "r1_traffic.json"):
         try:
             with open(os.path.join(REPO, "profiles", name)) as f:
-                return int(json.load(f)[key]["dram_bytes"])
+                entry = json.load(f)[key]
+            val = int(entry["dram_bytes"])
         except Exception:
             continue
-    return None
+        if not with_source:
+            return val
+        try:
+            commit = subprocess.run(["git", "log", "-1", "--format=%h", "--", f"profiles/{name}"], cwd=REPO,
+                                    capture_output=True, text=True, timeout=10).stdout.strip() or None
+        except Exception:
+            commit = None
+        return val, {"file": f"profiles/{name}", "capture": entry.get("source"), "file_commit": commit,
+                     "note": "committed ncu --set full capture, not measured by this run"}
+    return (None, None) if with_source else None
 
 
 def extend_flops(Hq, D, prefix, ext):
@@ -372,7 +384,11 @@ def measure_decode_workload(workload, rank, world, device, steps, warmup, oproj=
     # ---- e2e: the same step through the plugin call from pinned HOST buffers
     if with_e2e:
         qkv_host = [t.cpu().pin_memory() for t in qkv_dev]
-        out_host = [torch.empty(B, w["hidden"] if with_oproj else Hq * D, dtype=dt).pin_memory() for _ in range(L)]
+        # under TP the all-reduced result is replicated on every rank: each rank downloads its 1/N of the rows
+        rows = (rank * B // world, (rank + 1) * B // world) if tp else None
+        n_rows_host = rows[1] - rows[0] if tp else B
+        out_host = [torch.empty(n_rows_host, w["hidden"] if with_oproj else Hq * D, dtype=dt).pin_memory()
+                    for _ in range(L)]
         ids_host = torch.zeros(B, dtype=torch.int64).pin_memory()
         rpi_host, seq_host = w["rpi"].cpu().pin_memory(), w["seq"].cpu().pin_memory()
         loc_host = w["out_cache_loc"].cpu().pin_memory()
@@ -387,12 +403,13 @@ def measure_decode_workload(workload, rank, world, device, steps, warmup, oproj=
                 input_ids=ids, req_pool_indices=rpi, seq_lens=seq, out_cache_loc=loc,
                 req_to_token_pool=w["r2t_pool"], token_to_kv_pool=w["kv_pool"])
             # uploads of layer l+1 and downloads of layer l overlap layer l's kernels (host_staging.py)
-            staged.forward_layers(qkv_host, out_host, w["layers"], fb, after=after_attention if with_oproj else None)
+            staged.forward_layers(qkv_host, out_host, w["layers"], fb, after=after_attention if with_oproj else None,
+                                  out_rows=rows)
             return out_host[L - 1]
 
         res["ms_e2e"], _ = timed(step_e2e, steps, warmup)
-        res["h2d"] = sum(t.numel() * t.element_size() for t in qkv_host) + 8 * B * 3 + 4 * B
-        res["d2h"] = sum(t.numel() * t.element_size() for t in out_host)
+        res["h2d"] = (sum(t.numel() * t.element_size() for t in qkv_host) + 8 * B * 3 + 4 * B) * world   # whole job
+        res["d2h"] = sum(t.numel() * t.element_size() for t in out_host) * world   # whole job
         del qkv_host, out_host, staged
 
     # ---- roofline of the dominant kernel: paged_attention_kernel alone, CUDA events per launch
@@ -727,6 +744,7 @@ def run_b200(args, rank, world, device):
             "k2_ms_per_rank": round(s["k_ms"], 5),
             "k2_frac_of_hbm_peak": round(s["k_bytes"] / s["k_ms"] / 1e6 / peak, 4),
             "allreduce": s["allreduce"], "parity_check": s["parity_check"]}
+    tp_parity = measure_tp_parity(rank, world, device) if (world > 1 and not args.skip_parity) else None
     tok = small = None
     if world == 1 and rank == 0:
         if args.workload == "ns" and not args.skip_model:
@@ -775,22 +793,79 @@ def run_b200(args, rank, world, device):
         "e2e": {"value": round(total / m["ms_e2e"] / 1e6, 1), "unit": "GB/s", "ms_per_step": round(m["ms_e2e"], 4),
                 "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": m["d2h"],
                 "api": "HostStagedAttention.forward_layers (dropin attn_backend.SimpleAttentionBackend.forward per "
-                       "layer) from pinned host q/k/v, copies on side streams"},
+                       "layer) from pinned host q/k/v, copies on side streams"
+                       + ("; each rank uploads its own heads' q/k/v and downloads 1/N of the rows of the replicated "
+                          "all-reduced result" if tp else "")
+                       + ("; byte counts are sums over the ranks" if world > 1 else "")},
         "gpu_launches": m["launches"],
         "clocks": m["clocks"],
         "roofline": {"bound": "hbm", "kernel": "paged_attention_kernel", "achieved": round(achieved, 1),
                      "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "peak_source": peak_src,
                      "bytes_per_launch": m["k_bytes"], "avg_launch_ms": round(m["k_ms"], 5),
                      "traffic": args.traffic if args.traffic is not None else
-                     (traffic_from_profiles(args.workload) if world == 1 else None)},
+                     (traffic_from_profiles(args.workload) if world == 1 else None),
+                     "traffic_source": ({"file": "--traffic flag"} if args.traffic is not None else
+                                        (traffic_from_profiles(args.workload, with_source=True)[1] if world == 1
+                                         else None))},
         "parity_check": m["parity_check"],
         "allreduce": m["allreduce"],
         "sharded": sharded,
+        "tp_parity": tp_parity,
         "extend_roofline": extend,
         "small_kernels": small,
         "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)
+    if tp_parity is not None and not tp_parity["ok"]:
+        raise SystemExit("tp_parity failed: " + json.dumps(tp_parity["failed"])[:2000])
+
+
+def measure_tp_parity(rank, world, device):
+    """The multi-GPU parity scripts (tests/multi_gpu_oproj.py, tests/multi_gpu_tp.py) run inside this torchrun job,
+    after every timed leg: K8 under both exchanges incl. graph replay and odd row counts, host-staged attention + K8,
+    K8 in row blocks, and the reference's unchanged scheduler + model sharded by tp_runtime (NCCL / K8 / K8 + TP MLP
+    / row blocks) against the unsharded drop-in stack.  Their per-case JSON lines are collected, not printed."""
+    import contextlib
+    import io
+    from baseline import ref_loader
+    from tests import multi_gpu_oproj, multi_gpu_tp
+    group = torch.distributed.group.WORLD
+    saved = os.environ.get("BSGL_K8_EXCHANGE")
+    buf, ok, t0 = io.StringIO(), True, time.perf_counter()
+    skipped = []
+    try:
+        with contextlib.redirect_stdout(buf):
+            ok &= bool(multi_gpu_oproj.run("", rank, world, group))
+            ok &= bool(multi_gpu_oproj.run("nvls", rank, world, group))
+            ok &= bool(multi_gpu_oproj.host_staged(rank, world, group))
+            ok &= bool(multi_gpu_oproj.chunked(rank, world, group))
+            os.environ["BSGL_K8_EXCHANGE"] = ""
+            if ref_loader.find_reference() is None:
+                skipped.append("tp-sharded reference stack: no staged reference checkout")
+            elif multi_gpu_tp.CFG["num_key_value_heads"] % world:
+                skipped.append(f"tp-sharded reference stack: 8 KV heads do not shard over {world} ranks")
+            else:
+                ok &= bool(multi_gpu_tp.check(rank, world, group))
+    finally:
+        if saved is None:
+            os.environ.pop("BSGL_K8_EXCHANGE", None)
+        else:
+            os.environ["BSGL_K8_EXCHANGE"] = saved
+    flag = torch.tensor([1 if ok else 0], device=device)
+    torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MIN)
+    cases = []
+    for ln in buf.getvalue().splitlines():
+        try:
+            cases.append(json.loads(ln))
+        except ValueError:
+            pass
+    failed = [c for c in cases if not c.get("ok", True)]
+    _free()
+    return {"world": world, "cases": len(cases), "ok": bool(flag.item()) and not failed, "failed": failed[:4],
+            "skipped": skipped, "seconds": round(time.perf_counter() - t0, 1),
+            "what": "tests/multi_gpu_oproj.py (K8 both exchanges, 3 eager calls + 3 graph replays per shape, "
+                    "host-staged + K8, row blocks) and tests/multi_gpu_tp.py (unchanged scheduler + model, TP-sharded, "
+                    "4 variants x cold / radix-hit x 32 teacher-forced steps) inside this job, all ranks"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -930,7 +1005,7 @@ def main():
                          "F.linear + NCCL all-reduce")
     ap.add_argument("--traffic", type=float, default=None,
                     help="dram bytes per launch of the dominant kernel from an ncu --set full capture (profiles/)")
-    for flag in ("extend", "sharded", "model", "small"):
+    for flag in ("extend", "sharded", "model", "small", "parity"):
         ap.add_argument(f"--skip-{flag}", action="store_true", help=f"leave the `{flag}` leg out (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

@@ -53,13 +53,8 @@ def _run(run, prompts, forced=None):
     return out
 
 
-def main():
-    if ref_loader.find_reference() is None:
-        print(json.dumps({"skipped": "no reference checkout (scripts/stage_reference.py)"}))
-        return 0
-    sys.path.insert(0, DROPIN_DIR)
-    import tp_runtime
-    rank, world, group = tp_runtime.init_tp()
+def check(rank, world, group):
+    """All variants on an initialised process group (also called by bench.py's `tp_parity` leg).  True if all pass."""
     g = torch.Generator().manual_seed(11)
     prompts = [torch.randint(0, CFG["vocab_size"], (n,), generator=g) for n in LENS]
     base = ref_stack.build(DROPIN_DIR, CFG, "cuda", torch.bfloat16, **POOL)
@@ -104,6 +99,17 @@ def main():
             run.comm.close()
         del run
         torch.cuda.empty_cache()
+    return ok
+
+
+def main():
+    if ref_loader.find_reference() is None:
+        print(json.dumps({"skipped": "no reference checkout (scripts/stage_reference.py)"}))
+        return 0
+    sys.path.insert(0, DROPIN_DIR)
+    import tp_runtime
+    rank, world, group = tp_runtime.init_tp()
+    ok = check(rank, world, group)
     dist.barrier(group=group)
     dist.destroy_process_group()
     return 0 if ok else 1
