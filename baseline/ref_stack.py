@@ -39,6 +39,29 @@ def deterministic_weights(model: torch.nn.Module, scale: float = 1.0) -> None:
             p.copy_(val.to(p.dtype))
 
 
+def peak_lm_head(model: torch.nn.Module, peak: float, stride: int = 389) -> torch.Tensor:
+    """Widen the top-1 / top-2 margins of a random-init model without taking the context out of the decision.
+
+    A random LM head gives logits ~ N(0, 1) over the vocabulary: the top two are a few bf16 ulps apart every few
+    dozen steps, and rounding noise then decides the argmax in ANY implementation.  Here row j of `lm_head` gets, on
+    top of its random part, a multiple of the embedding of token perm[j] (perm[j] = (stride * j + 1) mod V, stride
+    odd): the token whose embedding dominates the residual stream -- normally the current input token t -- lifts the
+    logit of its "successor" inv_perm[t] to about `peak` (in units of the random logits' standard deviation), while
+    attention and MLP outputs still move every logit.  With `peak` around 5.5 most steps follow the successor chain
+    with a wide margin, a few per cent are decided by the context-dependent random part, and near-ties become rare
+    enough that a whole 64-step batch without one exists.  Returns inv_perm (successor of each token)."""
+    emb = model.model.embed_tokens.weight
+    V, H = emb.shape
+    perm = (torch.arange(V) * stride + 1) % V
+    with torch.no_grad():
+        e = emb.float()
+        # h = x / rms(x) with x = embedding + four block outputs of comparable size: h . e is about H / sqrt(5)
+        model.lm_head.weight.add_((peak * (5.0 ** 0.5) / H) * e[perm].to(model.lm_head.weight.dtype))
+    inv = torch.empty(V, dtype=torch.long)
+    inv[perm] = torch.arange(V)
+    return inv
+
+
 def bf16_ulp(x: float) -> float:
     """Spacing of bf16 numbers at |x| (8 significant bits)."""
     return 2.0 ** (math.floor(math.log2(max(abs(x), 2.0 ** -126))) - 7)
@@ -186,7 +209,7 @@ class StackRun:
 
 def build(shadow_dir: Optional[str], cfg_kwargs: dict, device: str, dtype: torch.dtype, max_total_tokens: int,
           max_requests: int, hooks: Sequence[str] = (), listen: bool = True, init: str = "deterministic",
-          tp: Optional[dict] = None) -> StackRun:
+          tp: Optional[dict] = None, lm_head_peak: Optional[float] = None) -> StackRun:
     """Reference scheduler + model on `device`; `shadow_dir=None` is the pure reference, `DROPIN_DIR` the product.
     `hooks` ⊆ {"rope", "sampler", "prep", "graph"} installs the row-(f) kernels (baby_sglang_b200.model_hooks) on
     the instances.  `tp = dict(rank, world, group, fused: bool, mlp: bool)` shards the unchanged model with the
@@ -199,6 +222,8 @@ def build(shadow_dir: Optional[str], cfg_kwargs: dict, device: str, dtype: torch
     if init == "deterministic":
         model = st.qwen2.BabyQwen2ForCausalLM(cfg).float().eval()
         deterministic_weights(model)
+        if lm_head_peak is not None:
+            peak_lm_head(model, lm_head_peak)
         model = model.to(device=device, dtype=dtype)
     else:   # big geometries: construct on the device, default torch init, seeded
         torch.manual_seed(0)

@@ -513,8 +513,68 @@ def measure_decode_tok_s(device, steps=64, batch=256, ctx=4096):
            "state": "decode phase seeded directly (baseline/ref_stack.seed_decode_state): the reference's own "
                     "prefill would need 319 GB of logits at this size",
            "unit": "tok/s", "variants": {}}
+    # The PURE reference stack first (its own torch attention path: 28 x 256 SDPA calls and ~14 k host syncs per
+    # step), same GPU, same seeded state, N_FORCED free-running steps with every sampled token's
+    # top-1 / top-2 logits recorded: context for the tok/s numbers, and the trajectory + margins the drop-in
+    # stack's ids are classified against below.
+    N_FORCED = 4
+    pure = None
+    try:
+        ref = ref_stack.build(None, cfg, str(device), torch.bfloat16, **pool, listen=True, init="device")
+        ref_stack.seed_decode_state(ref, batch, ctx, 8, seed=0)
+        r = ref_stack.timed_decode_steps(ref, N_FORCED - 1, warmup=1)
+        med = statistics.median(r["host_ms"])
+        vals = ref.log.values()             # one [top1, top2] per sample_next_ids call: step-major, request-minor
+        assert len(vals) == N_FORCED * batch, (len(vals), N_FORCED, batch)
+        pure = {"ids": r["ids"], "margins": [[vals[s * batch + i] for s in range(N_FORCED)] for i in range(batch)]}
+        out["pure_reference_on_this_gpu"] = {
+            "ms_per_step_median": round(med, 1), "decode_tok_per_s": round(batch / (med / 1e3), 1),
+            "steps": N_FORCED - 1,
+            "note": "the reference's unmodified attn_backend/memory_pool/forward_batch (torch gathers + SDPA per "
+                    "request) under the same scheduler and model; context, not the baseline arm"}
+        del ref
+    except Exception as e:
+        out["pure_reference_on_this_gpu"] = {"error": repr(e)[:300]}
+    _free()
     run = ref_stack.build(DROPIN_DIR, cfg, str(device), torch.bfloat16, **pool, listen=False, init="device")
     model = run.model
+    if pure is not None:
+        # teacher-forced over N_FORCED steps of all `batch` requests: the drop-in stack is fed the reference's tokens
+        # and its OWN argmax at every step is compared with them; a difference is a tie if the reference's own
+        # top-1 / top-2 margin there is within 2 bf16 ulps, else a mismatch (which fails the run)
+        out["id_parity_vs_pure_reference"] = {}
+        for name, hooks in (("dropin", ()), ("dropin+K5K6K7", ("rope", "sampler", "prep"))):
+            sched = run.stack.scheduler.Scheduler(model, tokenizer=None)
+            run.scheduler = sched
+            model_hooks.uninstall_fused_rope_kv_store(model)
+            if "rope" in hooks:
+                model_hooks.install_fused_rope_kv_store(model)
+            if "sampler" in hooks:
+                model_hooks.install_batched_greedy_sampler(sched)
+            if "prep" in hooks:
+                model_hooks.install_device_batch_prep(sched)
+            ref_stack.seed_decode_state(run, batch, ctx, 8, seed=0)
+            reqs = list(sched.decoding_batch)
+            ref_ids = [[pure["ids"][s][i] for s in range(N_FORCED)] for i in range(batch)]
+            forcer = ref_stack.Forcer(sched)
+            # Forcer indexes `want` by len(output_ids): the seeded first token sits at position 0
+            forcer.start_run([q.input_ids for q in reqs], [[int(q.output_ids[0])] + ids for q, ids in zip(reqs, ref_ids)])
+            ref_stack.timed_decode_steps(run, N_FORCED - 1, warmup=1)
+            res = ref_stack.classify_forced(ref_ids, [list(x) for x in forcer.own], pure["margins"])
+            req_bad = {m["request"] for m in res["mismatches"]}
+            req_tied = {t["request"] for t in res["ties"]} - req_bad
+            out["id_parity_vs_pure_reference"][name] = {
+                "requests": batch, "steps_per_request": N_FORCED, "steps_total": res["steps_total"],
+                "steps_equal": res["steps_equal"], "equal": batch - len(req_bad) - len(req_tied),
+                "tied": len(req_tied),
+                "ties": [{"request": t["request"], "step": t["step"], "ref_margin": round(t["ref_margin"], 5),
+                          "tie_tolerance": round(t["tie_tolerance"], 5)} for t in res["ties"]][:32],
+                "mismatches": len(res["mismatches"]), "mismatch_detail": res["mismatches"][:4],
+                "rule": "teacher-forced; tie = pure reference's own top-1/top-2 margin <= 2 bf16 ulps at that step"}
+            model_hooks.uninstall_fused_rope_kv_store(model)
+            del sched, forcer
+            run.scheduler = None
+            _free()
     ids_ref = None
     for name, hooks in (("dropin", ()), ("dropin+K5K6K7", ("rope", "sampler", "prep")),
                         ("dropin+K5K6K7+cuda_graph", ("rope", "sampler", "prep", "graph"))):
@@ -552,21 +612,6 @@ def measure_decode_tok_s(device, steps=64, batch=256, ctx=4096):
     out["best_variant"] = [k for k, x in out["variants"].items() if x is best][0]
     del run, model
     _free()
-    # context only: the PURE reference stack (its own torch attention path: 28 x 256 SDPA calls and ~14 k host
-    # syncs per step) on the same GPU, same seeded state, a few steps
-    try:
-        ref = ref_stack.build(None, cfg, str(device), torch.bfloat16, **pool, listen=False, init="device")
-        ref_stack.seed_decode_state(ref, batch, ctx, 8, seed=0)
-        r = ref_stack.timed_decode_steps(ref, 3, warmup=1)
-        med = statistics.median(r["host_ms"])
-        out["pure_reference_on_this_gpu"] = {
-            "ms_per_step_median": round(med, 1), "decode_tok_per_s": round(batch / (med / 1e3), 1), "steps": 3,
-            "first_step_ids_identical_to_dropin": r["ids"][0] == ids_ref[0],
-            "note": "the reference's unmodified attn_backend/memory_pool/forward_batch (torch gathers + SDPA per "
-                    "request) under the same scheduler and model; context, not the baseline arm"}
-        del ref
-    except Exception as e:
-        out["pure_reference_on_this_gpu"] = {"error": repr(e)[:300]}
     _free()
     return out
 
@@ -816,6 +861,9 @@ def run_b200(args, rank, world, device):
         "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)
+    idp = (tok or {}).get("id_parity_vs_pure_reference") or {}
+    if any(v["mismatches"] for v in idp.values()):
+        raise SystemExit("greedy ids differ from the pure reference away from a tie: " + json.dumps(idp)[:2000])
     if tp_parity is not None and not tp_parity["ok"]:
         raise SystemExit("tp_parity failed: " + json.dumps(tp_parity["failed"])[:2000])
 

@@ -207,6 +207,58 @@ def test_unchanged_stack_on_dropins_matches_pure_reference(name, mode):
             del forced
 
 
+# Tie-free cases: the same geometries and prompt lengths, with the LM head "peaked" (ref_stack.peak_lm_head) so that
+# the PURE REFERENCE's own top-1 / top-2 margin stays far above rounding noise at every one of the 64 steps of every
+# request.  (peak, prompt seed) were chosen once from a probe of the pure reference alone (scripts/probe_margins.py,
+# profiles/r3_probe_margins_bf16.jsonl: smallest margin 15 / 22 bf16 ulps at peak 4.0, where the 1.5B-heads case
+# still has steps decided by the context-dependent part of the logits; >= 33 ulps at peak 5.0).  fp16 is the dtype the
+# reference itself picks on CUDA (model_loader.py:56-64).
+TIE_FREE = {
+    ("qwen1.5b_heads", "bf16"): (4.0, 1003), ("qwen7b_heads", "bf16"): (4.0, 1000),
+    ("qwen1.5b_heads", "fp16"): (5.0, 1000), ("qwen7b_heads", "fp16"): (5.0, 1000),
+}
+MIN_REF_MARGIN_ULPS = 4.0       # asserted about the reference BEFORE anything is compared (2 ulps is the tie rule)
+
+
+@needs_ref
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["normal", "overlap"])
+@pytest.mark.parametrize("name,dt", sorted(TIE_FREE))
+def test_tie_free_case_is_identical_for_all_64_steps(name, dt, mode):
+    """north_star, literally: greedy token IDs identical for 64 steps, free running, EVERY request, cold and
+    radix-hit, normal and overlap mode, on the drop-ins alone and with K5/K6/K7 and the CUDA graph installed --
+    no tie rule involved: `ties` must be empty because the reference's margins leave no room for one."""
+    cfg, lens = GEOMETRIES[name]
+    peak, seed = TIE_FREE[(name, dt)]
+    dtype = torch.bfloat16 if dt == "bf16" else torch.float16
+    prompts = _prompts(cfg["vocab_size"], lens, seed=seed)
+    ref = ref_stack.build(None, cfg, "cuda", dtype, **POOL, lm_head_peak=peak)
+    ref_runs = _run(ref, prompts, mode)
+    del ref
+    worst = min((t1 - t2) / ref_stack.bf16_ulp(max(abs(t1), 1.0))
+                for _, margins, _, _ in ref_runs for m in margins for t1, t2 in m)
+    assert all(len(m) == N_NEW for _, margins, _, _ in ref_runs for m in margins), "recorder lost a step"
+    assert worst > MIN_REF_MARGIN_ULPS, f"harness case is not tie-free: reference margin {worst} bf16 ulps"
+    for label, hooks in (("dropin", ()), ("dropin+K5K6K7", ("rope", "sampler", "prep")),
+                         ("dropin+K5K6K7+graph", ("rope", "sampler", "prep", "graph"))):
+        got = ref_stack.build(DROPIN_DIR, cfg, "cuda", dtype, **POOL, listen=False, hooks=hooks, lm_head_peak=peak)
+        got_runs = _run(got, prompts, mode)
+        del got
+        for phase, (r, g) in zip(("cold", "radix-hit"), zip(ref_runs, got_runs)):
+            (rids, rmarg, rstate, _), (gids, _, gstate, _) = r, g
+            same = sum(a == b for a, b in zip(rids, gids))
+            res = ref_stack.classify_divergence(rids, gids, rmarg)
+            _append_flip_log({"case": f"{name}/{dt}/{mode}/{label}/tie-free/{phase}", "steps_total": res["steps_total"],
+                              "identical_requests": same, "requests": len(rids), "ties": res["ties"],
+                              "mismatches": res["mismatches"], "reference_min_margin_bf16_ulps": round(worst, 2)})
+            assert all(len(x) == N_NEW for x in gids)
+            assert gids == rids, f"{name} {dt} {mode} {label} {phase}: {same}/{len(rids)} requests identical"
+            assert not res["ties"] and not res["mismatches"]
+            _same_state(f"{name}/{dt}/{mode}/{label}", phase, rstate, gstate)
+        print(f"[real-stack] {name} {dt} {mode} {label}: {len(prompts)}/{len(prompts)} requests identical for "
+              f"{N_NEW} free-running steps, cold and radix-hit; reference min margin {worst:.1f} bf16 ulps")
+
+
 @needs_ref
 @pytest.mark.gpu
 def test_unchanged_stack_shared_prefixes_and_eviction():
