@@ -617,6 +617,143 @@ def measure_decode_tok_s(device, steps=64, batch=256, ctx=4096):
 
 
 # ------------------------------------------------------------------------------------------------
+# BASELINE.json configs[0] (C1): the one configuration the reference runs itself -- Qwen2.5-1.5B random
+# init, 8 x 512-token prompts, 64 greedy tokens through Scheduler.run_batch on CPU in fp32 -- timed beside the same
+# run_batch on the drop-in modules on the GPU, token ids compared
+# ------------------------------------------------------------------------------------------------
+def _timed_run_batch(run, prompts, sp, device_events, time_attention=True):
+    """One `Scheduler.run_batch` (scheduler.py:99-163) with a timestamp at every `_select_batch_to_run` (= step
+    boundary) and the time spent inside `SimpleAttentionBackend.forward` (attn_backend.py:8-32: KV store + attention,
+    every layer) accumulated per step: host clock on CPU, CUDA events on the GPU."""
+    sched, cls = run.scheduler, run.stack.qwen2.SimpleAttentionBackend
+    inner_fwd, inner_sel = cls.forward, sched._select_batch_to_run
+    marks, attn, modes, pending = [], [0.0], [], []
+
+    def fwd(*a, **kw):
+        if device_events:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            out = inner_fwd(*a, **kw)
+            e1.record()
+            pending.append((len(attn) - 1, e0, e1))
+            return out
+        t0 = time.perf_counter()
+        out = inner_fwd(*a, **kw)
+        attn[-1] += time.perf_counter() - t0
+        return out
+
+    def sel():
+        marks.append(time.perf_counter())
+        attn.append(0.0)
+        r = inner_sel()
+        modes.append(r[1])
+        return r
+
+    if time_attention:      # not under the CUDA-graph hook: timing events cannot be recorded inside a capture
+        cls.forward = staticmethod(fwd)
+    sched._select_batch_to_run = sel
+    try:
+        ids = sched.run_batch([p.clone() for p in prompts], sp)
+        if device_events:
+            torch.cuda.synchronize()
+        marks.append(time.perf_counter())
+    finally:
+        cls.forward = staticmethod(inner_fwd)
+        sched._select_batch_to_run = inner_sel
+    for i, e0, e1 in pending:
+        attn[i] += e0.elapsed_time(e1) / 1e3
+    steps = [b - a for a, b in zip(marks, marks[1:])]
+    attn = attn[1:]
+    dec = [i for i, m in enumerate(modes) if m == "decode"]
+    pre = [i for i, m in enumerate(modes) if m == "prefill"]
+    n_tok = sum(len(x) for x in ids)
+    return [[int(t) for t in r] for r in ids], {
+        "total_s": round(marks[-1] - marks[0], 3), "tok_per_s": round(n_tok / (marks[-1] - marks[0]), 1),
+        "prefill_s": round(sum(steps[i] for i in pre), 3), "prefill_attention_s": round(sum(attn[i] for i in pre), 4),
+        "decode_steps": len(dec),
+        "decode_ms_per_step_median": round(statistics.median(steps[i] for i in dec) * 1e3, 3),
+        "decode_attention_ms_per_step_median":
+            round(statistics.median(attn[i] for i in dec) * 1e3, 3) if time_attention else None,
+        "decode_attention_share":
+            round(sum(attn[i] for i in dec) / max(sum(steps[i] for i in dec), 1e-9), 3) if time_attention else None}
+
+
+def measure_c1(device, batch=8, ctx=512, new=64):
+    from baby_sglang_b200 import DROPIN_DIR
+    from baseline import ref_loader, ref_stack
+    if ref_loader.find_reference() is None:
+        return {"unavailable": "no reference checkout (baseline/_ref not staged: scripts/stage_reference.py)"}
+    Hq, Hkv, D, L, hidden, inter, vocab = GEOMETRY["qwen2.5-1.5b"]
+    cfg = dict(hidden_size=hidden, num_attention_heads=Hq, num_key_value_heads=Hkv, intermediate_size=inter,
+               num_hidden_layers=L, vocab_size=vocab, tie_word_embeddings=True)
+    pool = dict(max_total_tokens=2 * batch * (ctx + new), max_requests=batch)
+    g = torch.Generator().manual_seed(2025)
+    prompts = [torch.randint(0, vocab, (ctx,), generator=g) for _ in range(batch)]
+    out = {"workload": f"BASELINE.json configs[0]: qwen2.5-1.5b geometry ({Hq}q/{Hkv}kv, D={D}, {L} layers, vocab "
+                       f"{vocab}), random init, {batch} x {ctx}-token prompts, {new} greedy tokens each through the "
+                       f"reference's unchanged Scheduler.run_batch (scheduler.py:99-163)"}
+    # ---- the reference itself: CPU, fp32 (model_loader.py:56-64 picks fp32 on CPU), all host threads
+    ref = ref_stack.build(None, cfg, "cpu", torch.float32, **pool, listen=True, init="device")
+    sp = ref.stack.sample.SamplingParams(max_new_tokens=new, do_sample=False, eos_id=-1)
+    ref.tracker.start_run()
+    cpu_ids, cpu_t = _timed_run_batch(ref, prompts, sp, device_events=False)
+    cpu_margins = ref.tracker.margins(prompts)
+    out["reference_cpu_fp32"] = {**cpu_t, "cores": torch.get_num_threads(),
+                                 "impl": "unmodified reference stack (staged checkout), torch CPU kernels"}
+    weights = {k: v.to(torch.bfloat16) if v.is_floating_point() else v for k, v in ref.model.state_dict().items()}
+    del ref
+    gc.collect()
+
+    def gpu_stack(shadow, hooks=(), listen=False):
+        r = ref_stack.build(shadow, cfg, str(device), torch.bfloat16, **pool, listen=listen, init="device", hooks=hooks)
+        r.model.load_state_dict(weights, strict=False)       # the SAME random weights as the CPU run, rounded to bf16
+        return r
+
+    # ---- the pure reference on this GPU in bf16 (its own torch attention path): trajectory + margins to classify against
+    gref = gpu_stack(None, listen=True)
+    gref.tracker.start_run()
+    gref_ids, gref_t = _timed_run_batch(gref, prompts, sp, device_events=True)
+    gref_margins = gref.tracker.margins(prompts)
+    out["pure_reference_gpu_bf16"] = gref_t
+    del gref
+    _free()
+    # ---- the drop-in modules under the same scheduler and model
+    for name, hooks in (("dropin", ()), ("dropin+K5K6K7+cuda_graph", ("rope", "sampler", "prep", "graph"))):
+        got = gpu_stack(DROPIN_DIR, hooks=hooks)
+        ta = not hooks
+        _timed_run_batch(got, prompts, sp, True, time_attention=ta)           # warm-up (module loads, graph capture)
+        ids, t = _timed_run_batch(got, prompts, sp, True, time_attention=ta)  # radix-hit rerun of the same prompts
+        free = ref_stack.classify_divergence(gref_ids, ids, gref_margins)
+        forcer = ref_stack.Forcer(got.scheduler)
+        forcer.start_run(prompts, gref_ids)
+        got.scheduler.run_batch([p.clone() for p in prompts], sp)
+        forced = ref_stack.classify_forced(gref_ids, [list(x) for x in forcer.own], gref_margins)
+        vs_cpu = ref_stack.classify_forced(cpu_ids, [list(x) for x in forcer.own], cpu_margins) \
+            if cpu_ids == gref_ids else None
+        t["ids_vs_pure_reference_gpu_bf16"] = {
+            "requests": batch, "steps_total": forced["steps_total"],
+            "free_running_identical_requests": sum(a == b for a, b in zip(gref_ids, ids)),
+            "free_running_tie_departures": len(free["ties"]), "free_running_mismatches": len(free["mismatches"]),
+            "teacher_forced_steps_equal": forced["steps_equal"], "teacher_forced_ties": len(forced["ties"]),
+            "teacher_forced_mismatches": len(forced["mismatches"]), "mismatch_detail": forced["mismatches"][:3],
+            "rule": "tie = the pure reference's own top-1/top-2 margin <= 2 bf16 ulps at that step"}
+        t["note"] = "timed on the second run_batch call (radix hit on the whole prompt, like any repeated prompt)"
+        if vs_cpu is not None:
+            t["ids_vs_reference_cpu_fp32_teacher_forced"] = {"steps_equal": vs_cpu["steps_equal"],
+                                                             "steps_total": vs_cpu["steps_total"]}
+        out[name] = t
+        del got, forcer
+        _free()
+    same = sum(a == b for a, b in zip(cpu_ids, gref_ids))
+    out["reference_cpu_fp32_vs_reference_gpu_bf16"] = {
+        "identical_requests_free_running": same, "requests": batch,
+        "note": "the reference against itself across dtype/device: fp32 CPU vs bf16 GPU trajectories part wherever "
+                "28 layers of bf16 rounding outweigh a margin; the drop-ins are therefore classified against the "
+                "reference run in their own dtype on the same GPU"}
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
 # K1 / K5 / K6: HBM-bound byte kernels either side of the path
 # ------------------------------------------------------------------------------------------------
 def measure_small_kernels(device):
@@ -790,7 +927,7 @@ def run_b200(args, rank, world, device):
             "k2_frac_of_hbm_peak": round(s["k_bytes"] / s["k_ms"] / 1e6 / peak, 4),
             "allreduce": s["allreduce"], "parity_check": s["parity_check"]}
     tp_parity = measure_tp_parity(rank, world, device) if (world > 1 and not args.skip_parity) else None
-    tok = small = None
+    tok = small = configs = None
     if world == 1 and rank == 0:
         if args.workload == "ns" and not args.skip_model:
             try:
@@ -801,6 +938,33 @@ def run_b200(args, rank, world, device):
         if not args.skip_small:
             small = measure_small_kernels(device)
             small["small_batch_decode"] = measure_small_batch(device)
+        if args.workload == "ns" and not args.skip_configs:
+            # BASELINE.json configs[1] (C2) and configs[3] (C4) in the same driver-run line: K2 alone (CUDA events
+            # per launch) against the measured HBM peak, the whole step, and a sampled parity check vs the oracle
+            peak, _ = peaks()
+            configs = {}
+            for wl, n_steps in (("c2", 10), ("c4", 5)):
+                _free()
+                try:
+                    c = measure_decode_workload(wl, rank, world, device, n_steps, 3, with_e2e=False, roof_reps=3)
+                    model_name, cB, clo, chi, cL = WORKLOADS[wl]
+                    configs[wl] = {
+                        "workload": f"{model_name} paged GQA decode ({c['Hq']}q/{c['Hkv']}kv, D={c['D']}), batch {cB}, "
+                                    f"ctx {clo}..{chi}, {cL} layer(s) resident per step",
+                        "k2_ms": round(c["k_ms"], 5), "k2_bytes_per_launch": c["k_bytes"],
+                        "k2_GBps": round(c["k_bytes"] / c["k_ms"] / 1e6, 1),
+                        "frac": round(c["k_bytes"] / c["k_ms"] / 1e6 / peak, 4),
+                        "ms_per_step": round(c["ms_step"], 4),
+                        "step_GBps": round(c["step_bytes"] / c["ms_step"] / 1e6, 1),
+                        "traffic": traffic_from_profiles(wl), "parity_check": c["parity_check"]}
+                except Exception as e:
+                    configs[wl] = {"error": repr(e)[:400]}
+            _free()
+            try:
+                configs["c1"] = measure_c1(device)
+            except Exception as e:
+                configs["c1"] = {"error": repr(e)[:600]}
+            _free()
     if rank != 0:
         return
     cpu = cpu_baseline(args.workload, seconds=15.0)
@@ -858,9 +1022,15 @@ def run_b200(args, rank, world, device):
         "tp_parity": tp_parity,
         "extend_roofline": extend,
         "small_kernels": small,
+        "configs": configs,
         "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)
+    c1 = (configs or {}).get("c1") or {}
+    c1_bad = [k for k, v in c1.items() if isinstance(v, dict) and
+              (v.get("ids_vs_pure_reference_gpu_bf16") or {}).get("teacher_forced_mismatches")]
+    if c1_bad:
+        raise SystemExit("C1: greedy ids differ from the pure reference away from a tie: " + json.dumps(c1_bad))
     idp = (tok or {}).get("id_parity_vs_pure_reference") or {}
     if any(v["mismatches"] for v in idp.values()):
         raise SystemExit("greedy ids differ from the pure reference away from a tie: " + json.dumps(idp)[:2000])
@@ -1053,7 +1223,7 @@ def main():
                          "F.linear + NCCL all-reduce")
     ap.add_argument("--traffic", type=float, default=None,
                     help="dram bytes per launch of the dominant kernel from an ncu --set full capture (profiles/)")
-    for flag in ("extend", "sharded", "model", "small", "parity"):
+    for flag in ("extend", "sharded", "model", "small", "parity", "configs"):
         ap.add_argument(f"--skip-{flag}", action="store_true", help=f"leave the `{flag}` leg out (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
