@@ -295,7 +295,7 @@ def measure_extend_c3(device, reps=20):
 
 
 def measure_decode_workload(workload, rank, world, device, steps, warmup, oproj="fused", sample_clocks=False,
-                            with_e2e=True, roof_reps=None):
+                            with_e2e=True, roof_reps=None, force_oproj=False):
     """One decode workload under the sharding `tp_runtime.plan_parallelism` picks for `world`.  Returns a dict of
     measurements (times are the max over ranks)."""
     from baby_sglang_b200 import ops
@@ -313,11 +313,13 @@ def measure_decode_workload(workload, rank, world, device, steps, warmup, oproj=
         w = build_workload(workload, device, seed=1234 + rank)
     B, Hq, Hkv, D, L = w["B"], w["Hq"], w["Hkv"], w["D"], w["L"]
     dt = torch.bfloat16
-    with_oproj = tp or workload == "c5"       # the o_proj shard belongs to the step wherever a collective follows it
+    # the o_proj shard belongs to the step wherever a collective follows it; `force_oproj` adds the full o_proj (K8's
+    # world-1 form) to a single-GPU step so that it does the same work as the TP step it is compared with
+    with_oproj = tp or workload == "c5" or force_oproj
     tp_group = torch.distributed.group.WORLD if world > 1 else None
     w_o = torch.randn(w["hidden"], Hq * D, device=device, dtype=dt) * 0.02 if with_oproj else None
     fused_comm = None
-    if tp and oproj == "fused":   # K8: one kernel per rank instead of GEMM + NCCL call
+    if (tp or (force_oproj and world == 1)) and oproj == "fused":   # K8: one kernel per rank instead of GEMM + NCCL call
         fused_comm = tp_runtime.FusedOProjAllReduce(rank, world, tp_group, hidden=w["hidden"], max_tokens=B)
 
     def nccl_pair(out):
@@ -926,6 +928,27 @@ def run_b200(args, rank, world, device):
             "k2_ms_per_rank": round(s["k_ms"], 5),
             "k2_frac_of_hbm_peak": round(s["k_bytes"] / s["k_ms"] / 1e6 / peak, 4),
             "allreduce": s["allreduce"], "parity_check": s["parity_check"]}
+    # The same work on ONE GPU, measured inside this job (rank 0 alone, the others wait): full heads + the full o_proj,
+    # so that the TP step is compared with a single-GPU step that also pays for the GEMM
+    tp1 = None
+    if world > 1 and main["tp"] and not args.skip_tp1:
+        if rank == 0:
+            _free()
+            a = measure_decode_workload(args.workload, 0, 1, device, max(5, args.steps // 2), 3, oproj=args.oproj,
+                                        with_e2e=False, roof_reps=1, force_oproj=True)
+            tp1 = {"ms_per_step": round(a["ms_step"], 4), "oproj": "K8 world-1 form (full o_proj, no exchange)",
+                   "speedup_of_this_run": round(a["ms_step"] / main["ms_step"], 3),
+                   "efficiency_of_this_run": round(a["ms_step"] / main["ms_step"] / world, 3),
+                   "note": "rank 0 alone, same job, same step as the TP ranks run (K4 + per layer K1, K2, K2c, o_proj) "
+                           "on all heads of all requests"}
+            if sharded is not None and sharded.get("parallelism", "").startswith("KV-head TP"):
+                b = measure_decode_workload("c5", 0, 1, device, 5, 3, oproj=args.oproj, with_e2e=False, roof_reps=1,
+                                            force_oproj=True)
+                sharded["tp1_ms_per_step_same_job"] = round(b["ms_step"], 4)
+                sharded["speedup_vs_tp1"] = round(b["ms_step"] / sharded["ms_per_step"], 3)
+                sharded["efficiency"] = round(b["ms_step"] / sharded["ms_per_step"] / world, 3)
+            _free()
+        torch.distributed.barrier()
     tp_parity = measure_tp_parity(rank, world, device) if (world > 1 and not args.skip_parity) else None
     tok = small = configs = None
     if world == 1 and rank == 0:
@@ -1019,6 +1042,7 @@ def run_b200(args, rank, world, device):
         "parity_check": m["parity_check"],
         "allreduce": m["allreduce"],
         "sharded": sharded,
+        "tp1_same_work": tp1,
         "tp_parity": tp_parity,
         "extend_roofline": extend,
         "small_kernels": small,
@@ -1223,7 +1247,7 @@ def main():
                          "F.linear + NCCL all-reduce")
     ap.add_argument("--traffic", type=float, default=None,
                     help="dram bytes per launch of the dominant kernel from an ncu --set full capture (profiles/)")
-    for flag in ("extend", "sharded", "model", "small", "parity", "configs"):
+    for flag in ("extend", "sharded", "model", "small", "parity", "configs", "tp1"):
         ap.add_argument(f"--skip-{flag}", action="store_true", help=f"leave the `{flag}` leg out (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
