@@ -933,6 +933,7 @@ def run_b200(args, rank, world, device):
     tp1 = None
     if world > 1 and main["tp"] and not args.skip_tp1:
         if rank == 0:
+          try:       # a failure here must not leave the other ranks waiting at the barrier below
             _free()
             a = measure_decode_workload(args.workload, 0, 1, device, max(5, args.steps // 2), 3, oproj=args.oproj,
                                         with_e2e=False, roof_reps=1, force_oproj=True)
@@ -947,6 +948,9 @@ def run_b200(args, rank, world, device):
                 sharded["tp1_ms_per_step_same_job"] = round(b["ms_step"], 4)
                 sharded["speedup_vs_tp1"] = round(b["ms_step"] / sharded["ms_per_step"], 3)
                 sharded["efficiency"] = round(b["ms_step"] / sharded["ms_per_step"] / world, 3)
+            _free()
+          except Exception as e:
+            tp1 = {"error": repr(e)[:400]}
             _free()
         torch.distributed.barrier()
     tp_parity = measure_tp_parity(rank, world, device) if (world > 1 and not args.skip_parity) else None
